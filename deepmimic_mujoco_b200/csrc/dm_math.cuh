@@ -1,0 +1,168 @@
+// Scalar helpers shared by the generated forward kinematics and the step logic.
+// Everything is templated on the scalar type: float in the per-step kernel, double in the
+// clip-table builder.  The file also compiles as plain C++ (tests/host_harness builds it with
+// g++ to unit-test the arithmetic on machines without a GPU); the shipped library is CUDA only.
+#pragma once
+#include <cmath>
+#include <cstdint>
+
+#if defined(__CUDACC__)
+#define DM_HD __host__ __device__ __forceinline__
+#else
+#define DM_HD inline
+#endif
+
+namespace dm {
+
+template <typename T>
+struct FkOut {
+  T rq[4];        // root (free joint) quaternion after mj_normalizeQuat, wxyz
+  T tq[4];        // torso body xquat
+  T com[3];       // sum(m * xipos) / sum(m)   (mass_center / subtree_com of the root)
+  T com_xpos[3];  // sum(m * xpos) / sum(m)    (the reward's "C.O.M", deepmimic_env.py:235-238)
+  T ee[12];       // 4 end-effector geom_xpos, RobotConfig.endeffector_geom_names order
+  T cvel[6];      // torso cvel: [angular; linear]
+};
+
+struct NullSink {
+  static constexpr bool kWantsGeoms = false;
+  template <typename T> DM_HD void body(int, T, T, T) {}
+  template <typename T> DM_HD void geom(int, T, T, T) {}
+};
+
+DM_HD float dm_fma(float a, float b, float c) { return fmaf(a, b, c); }
+DM_HD double dm_fma(double a, double b, double c) { return fma(a, b, c); }
+
+// sin and cos of theta / 2 (hinge half-angle)
+DM_HD void dm_sincos_half(float theta, float& s, float& c) {
+#if defined(__CUDA_ARCH__)
+  sincosf(0.5f * theta, &s, &c);
+#else
+  s = sinf(0.5f * theta);
+  c = cosf(0.5f * theta);
+#endif
+}
+DM_HD void dm_sincos_half(double theta, double& s, double& c) {
+  s = sin(0.5 * theta);
+  c = cos(0.5 * theta);
+}
+
+DM_HD float dm_rsqrt(float x) {
+#if defined(__CUDA_ARCH__)
+  return rsqrtf(x);
+#else
+  return 1.0f / sqrtf(x);
+#endif
+}
+DM_HD double dm_rsqrt(double x) { return 1.0 / sqrt(x); }
+
+// mju_normalize4: zero quaternion -> identity
+template <typename T>
+DM_HD void dm_normalize4(T& w, T& x, T& y, T& z) {
+  T n2 = w * w + x * x + y * y + z * z;
+  if (!(n2 >= T(1e-30))) {  // mjMINVAL^2; also catches NaN
+    if (n2 == n2) { w = T(1); x = T(0); y = T(0); z = T(0); }
+    return;
+  }
+  T inv = T(1) / sqrt(n2);
+  w *= inv; x *= inv; y *= inv; z *= inv;
+}
+
+// mju_quat2Mat
+template <typename T>
+DM_HD void dm_quat2mat(T w, T x, T y, T z, T& r00, T& r01, T& r02, T& r10, T& r11, T& r12, T& r20, T& r21, T& r22) {
+  T ww = w * w, xx = x * x, yy = y * y, zz = z * z;
+  T xy = x * y, xz = x * z, yz = y * z, wx = w * x, wy = w * y, wz = w * z;
+  r00 = ww + xx - yy - zz; r01 = T(2) * (xy - wz);   r02 = T(2) * (xz + wy);
+  r10 = T(2) * (xy + wz);  r11 = ww - xx + yy - zz;  r12 = T(2) * (yz - wx);
+  r20 = T(2) * (xz - wy);  r21 = T(2) * (yz + wx);   r22 = ww - xx - yy + zz;
+}
+// single columns of the same matrix (world direction of a body-frame coordinate axis)
+template <typename T>
+DM_HD void dm_quat_col0(T w, T x, T y, T z, T& a, T& b, T& c) {
+  a = w * w + x * x - y * y - z * z; b = T(2) * (x * y + w * z); c = T(2) * (x * z - w * y);
+}
+template <typename T>
+DM_HD void dm_quat_col1(T w, T x, T y, T z, T& a, T& b, T& c) {
+  a = T(2) * (x * y - w * z); b = w * w - x * x + y * y - z * z; c = T(2) * (y * z + w * x);
+}
+template <typename T>
+DM_HD void dm_quat_col2(T w, T x, T y, T z, T& a, T& b, T& c) {
+  a = T(2) * (x * z + w * y); b = T(2) * (y * z - w * x); c = w * w - x * x - y * y + z * z;
+}
+
+// q <- q * (c, s*e_k): hinge about a coordinate axis (mju_axisAngle2Quat + mju_mulQuat)
+template <typename T>
+DM_HD void dm_quat_hinge_x(T& w, T& x, T& y, T& z, T s, T c) {
+  T nw = w * c - x * s, nx = x * c + w * s, ny = y * c + z * s, nz = z * c - y * s;
+  w = nw; x = nx; y = ny; z = nz;
+}
+template <typename T>
+DM_HD void dm_quat_hinge_y(T& w, T& x, T& y, T& z, T s, T c) {
+  T nw = w * c - y * s, nx = x * c - z * s, ny = y * c + w * s, nz = z * c + x * s;
+  w = nw; x = nx; y = ny; z = nz;
+}
+template <typename T>
+DM_HD void dm_quat_hinge_z(T& w, T& x, T& y, T& z, T s, T c) {
+  T nw = w * c - z * s, nx = x * c + y * s, ny = y * c - x * s, nz = z * c + w * s;
+  w = nw; x = nx; y = ny; z = nz;
+}
+
+// py3dtf Quaternion(x, y, z, w).to_rpy() of a UNIT quaternion (see oracle/rotations.py:to_rpy)
+template <typename T>
+DM_HD void dm_rpy(T w, T x, T y, T z, T& roll, T& pitch, T& yaw) {
+  roll = atan2(T(2) * (w * x + y * z), T(1) - T(2) * (x * x + y * y));
+  T sp = T(2) * (w * y - z * x);
+  sp = sp > T(1) ? T(1) : (sp < T(-1) ? T(-1) : sp);
+  pitch = asin(sp);
+  yaw = atan2(T(2) * (w * z + x * y), T(1) - T(2) * (y * y + z * z));
+}
+template <typename T>
+DM_HD void dm_roll_pitch(T w, T x, T y, T z, T& roll, T& pitch) {
+  roll = atan2(T(2) * (w * x + y * z), T(1) - T(2) * (x * x + y * y));
+  T sp = T(2) * (w * y - z * x);
+  sp = sp > T(1) ? T(1) : (sp < T(-1) ? T(-1) : sp);
+  pitch = asin(sp);
+}
+
+// Roll / pitch / yaw of the RAW (fp32, not necessarily unit) free-joint quaternion.  Products of fp32
+// values are exact in double, so the atan2 arguments carry no cancellation error; that keeps roll and
+// yaw accurate next to gimbal lock (the face-down get-up poses sit at pitch ~ 90 deg), where the fp32
+// forms 1 - 2(x^2 + y^2) lose all their digits.  pitch uses atan2(sp, cp), which stays well conditioned.
+DM_HD void dm_rpy_raw(float wf, float xf, float yf, float zf, float& roll, float& pitch, float& yaw) {
+  const double w = wf, x = xf, y = yf, z = zf;
+  const double ww = w * w, xx = x * x, yy = y * y, zz = z * z;
+  const double n2 = (ww + xx) + (yy + zz);
+  const double rn = 2.0 * (w * x + y * z), rd = n2 - 2.0 * (xx + yy);
+  const double yn = 2.0 * (w * z + x * y), yd = n2 - 2.0 * (yy + zz);
+  const double sp = 2.0 * (w * y - z * x);
+  const double cp2 = yn * yn + yd * yd;  // = (n2 cos(pitch))^2
+  roll = atan2f((float)rn, (float)rd);
+  yaw = atan2f((float)yn, (float)yd);
+  pitch = atan2f((float)sp, sqrtf((float)cp2));
+  if (!(n2 >= 1e-30)) {  // mju_normalize4 turns a zero quaternion into identity
+    if (n2 == n2) { roll = 0.0f; pitch = 0.0f; yaw = 0.0f; }
+  }
+}
+
+// numpy max / min semantics: NaN propagates (np.max(obs) > 100 is False when any obs is NaN)
+DM_HD float dm_max_nan(float a, float b) {
+#if defined(__CUDA_ARCH__)
+  float r;
+  asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+#else
+  return (a != a || b != b) ? NAN : (a > b ? a : b);
+#endif
+}
+DM_HD float dm_min_nan(float a, float b) {
+#if defined(__CUDA_ARCH__)
+  float r;
+  asm("min.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+#else
+  return (a != a || b != b) ? NAN : (a < b ? a : b);
+#endif
+}
+
+}  // namespace dm

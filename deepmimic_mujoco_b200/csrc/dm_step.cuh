@@ -1,0 +1,307 @@
+// Per-environment step logic: observation, imitation reward, termination / motion state
+// machine, action -> motor torque.  One call handles ONE environment; the kernels in
+// dmhot.cu map environments onto threads and provide the `IO` accessor (global memory with
+// strides, or shared-memory tiles).  Reference: src/deepmimic_env.py:33-173 (get_obs),
+// :193-256 (calc_imitation_reward), :335-484 (DPEnv.step); src/combined_env.py:246-505
+// (DPCombinedEnv.step / _get_obs); restated for float64 in oracle/envs.py.
+#pragma once
+#include "dm_math.cuh"
+
+namespace dm {
+
+// ---- clip tables -------------------------------------------------------------------------
+// One packed fp32 row per mocap frame holding only what a step reads (all target-side
+// quantities are precomputed once per frame by the table builder):
+//   [0, NSEL)            q*   selected joint angles          (deepmimic_env.py:200,208)
+//   [NSEL, 2 NSEL)       v*   selected joint velocities      (:202,210)
+//   2 NSEL + 0, + 1      roll*, pitch* of the root quaternion (:218-219)
+//   2 NSEL + 2 .. + 13   4 end-effector geom_xpos*           (:232)
+//   2 NSEL + 14 .. + 16  COM* = sum(m * body_xpos*) / sum(m) (:235-237)
+//   2 NSEL + 17, + 18    root linear velocity v*_xy          (combined_env.py:344)
+// padded to a multiple of 4 floats so rows are 16-byte aligned.
+template <class Rb>
+struct RowLayout {
+  static constexpr int Q = 0, V = Rb::NSEL, ROLL = 2 * Rb::NSEL, PITCH = ROLL + 1, EE = ROLL + 2, COM = ROLL + 14,
+                       VXY = ROLL + 17, USED = ROLL + 19, STRIDE = (USED + 3) / 4 * 4;
+};
+
+enum : int { CLIP_FLOOR = 1, CLIP_ACYCLIC = 2, CLIP_G1_RUN = 4 };
+enum : int { KIND_SINGLE = 0, KIND_COMBINED = 1 };
+enum : int { C_WALK = 0, C_RUN = 1, C_GETUP = 2, C_TO_GETUP = 3 };
+enum : int { R_NONE = 0, R_LOW_Z, R_HIGH_Z, R_RUN_ROLL, R_RUN_PITCH, R_MAX_EP, R_ACYC_END, R_FALLEN, R_OBS_BOUNDS };
+
+struct ClipDesc {
+  int row0;       // first row of this clip in the packed table
+  int len;        // get_length()
+  int flags;      // CLIP_*
+  int fixed_row;  // >= 0: constant-pose clip (MotionTransition: always frame 1), else -1
+};
+constexpr int kMaxClips = 8;
+struct ClipSet {
+  const float* rows;
+  int n_clips;
+  ClipDesc clip[kMaxClips];
+};
+
+template <int KIND, class Rb>
+struct ObsLayout;
+template <class Rb>
+struct ObsLayout<KIND_SINGLE, Rb> {  // DPEnvConfig: torso, foot contact, phase
+  static constexpr int TORSO = 2 * Rb::NJ, CONTACT = TORSO + 8, NCONTACT = 2, PHASE = CONTACT + 2, PA = PHASE + 1,
+                       DIM = PHASE + 1;
+  static constexpr int MAX_EP = 1000;
+};
+template <class Rb>
+struct ObsLayout<KIND_COMBINED, Rb> {  // DPCombinedEnvConfig: torso, extra contact, phase, player action
+  static constexpr int TORSO = 2 * Rb::NJ, CONTACT = TORSO + 8, NCONTACT = 8, PHASE = CONTACT + 8, PA = PHASE + 1,
+                       DIM = PA + 7;
+  static constexpr int MAX_EP = 2000;
+};
+
+constexpr double kDeg60 = 1.0471975511965976;  // np.deg2rad(60.)
+constexpr double kDeg15 = 0.2617993877991494;  // np.deg2rad(15)
+constexpr int kAmnestySteps = 150;             // combined_env.py:35
+
+struct EnvState {
+  int idx;     // single: idx_curr;  combined: current_motion_n_steps
+  int ep_len;  // episode_length
+  int clip;    // clip id (single: fixed per env; combined: motion state)
+};
+
+struct StepOut {
+  float reward;
+  float raw_reward;  // reward before the obs-bounds guard zeroed it (the reference adds this to episode_reward)
+  uint8_t done;
+  uint8_t reason;
+  float terms[8];  // reward_config, reward_qvel, reward_end_eff, reward_com, reward_joint_limit,
+                   // imitation_reward, task_reward, z_com
+};
+
+// ---- observation (get_obs) -----------------------------------------------------------------
+// Writes the DIM observation values through io.obs(j, v) and returns max / min with numpy's
+// NaN-propagating semantics for the bounds guard.
+template <int KIND, class Rb, class IO>
+DM_HD void write_obs(IO& io, const FkOut<float>& fk, const float* root_rpy, uint32_t contact, int frame, int len,
+                     int clip, float& omax, float& omin) {
+  using L = ObsLayout<KIND, Rb>;
+  float mx = -INFINITY, mn = INFINITY;
+  auto put = [&](int j, float v) {
+    io.obs(j, v);
+    mx = dm_max_nan(mx, v);
+    mn = dm_min_nan(mn, v);
+  };
+#pragma unroll
+  for (int j = 0; j < Rb::NJ; ++j) put(j, io.qpos(7 + j));
+#pragma unroll
+  for (int j = 0; j < Rb::NJ; ++j) put(Rb::NJ + j, io.qvel(6 + j) * 0.1f);
+  // torso block (deepmimic_env.py:47-76): rpy of the torso quaternion, yaw-aligned linear velocity
+  float roll, pitch, yaw;
+  if (Rb::kTorsoIsRoot) {  // torso body carries the free joint: its xquat is the normalised qpos[3:7]
+    roll = root_rpy[0]; pitch = root_rpy[1]; yaw = root_rpy[2];
+  } else {
+    dm_rpy(fk.tq[0], fk.tq[1], fk.tq[2], fk.tq[3], roll, pitch, yaw);
+  }
+  float sy, cy;
+#if defined(__CUDA_ARCH__)
+  sincosf(-yaw, &sy, &cy);
+#else
+  sy = sinf(-yaw);
+  cy = cosf(-yaw);
+#endif
+  const float vx = cy * fk.cvel[3] - sy * fk.cvel[4];
+  const float vy = sy * fk.cvel[3] + cy * fk.cvel[4];
+  put(L::TORSO + 0, roll * 0.1f);
+  put(L::TORSO + 1, pitch * 0.1f);
+  put(L::TORSO + 2, vx * 0.1f);
+  put(L::TORSO + 3, vy * 0.1f);
+  put(L::TORSO + 4, fk.cvel[5] * 0.1f);
+  put(L::TORSO + 5, fk.cvel[0] * 0.1f);
+  put(L::TORSO + 6, fk.cvel[1] * 0.1f);
+  put(L::TORSO + 7, fk.cvel[2] * 0.1f);
+  if (KIND == KIND_SINGLE) {  // [rfoot & floor, lfoot & floor] (:78-105)
+    put(L::CONTACT + 0, (contact & 1u) ? 1.0f : 0.0f);
+    put(L::CONTACT + 1, (contact & 2u) ? 1.0f : 0.0f);
+  } else {  // eight extra-contact geoms & floor (:107-121)
+#pragma unroll
+    for (int k = 0; k < 8; ++k) put(L::CONTACT + k, ((contact >> (2 + k)) & 1u) ? 1.0f : 0.0f);
+  }
+  float ph = float(frame) / float(len);  // :139-143
+  ph = ph < 0.0f ? 0.0f : (ph > 1.0f ? 1.0f : ph);
+  put(L::PHASE, ph);
+  if (KIND == KIND_COMBINED) {  // :145-173 with PAWalk heading (1, 0, 0): hx = cos(-yaw), hy = sin(-yaw)
+    put(L::PA + 0, cy);
+    put(L::PA + 1, sy);
+    put(L::PA + 2, 1.0f);  // onehot('walk'); PA resampling is disabled (combined_env.py:303)
+    put(L::PA + 3, 0.0f);
+    put(L::PA + 4, 0.0f);
+    put(L::PA + 5, clip == C_TO_GETUP ? 1.0f : 0.0f);  // pa_getup_state (combined_env.py:499-504)
+    put(L::PA + 6, clip == C_GETUP ? 1.0f : 0.0f);
+  }
+  omax = mx;
+  omin = mn;
+}
+
+// ---- action -> motor torque (deepmimic_env.py:347-352 + MuJoCo <motor>) ----------------------
+template <class Rb, class IO>
+DM_HD void write_torque(IO& io) {
+#pragma unroll
+  for (int k = 0; k < Rb::NU; ++k) {
+    float t = 0.0f;
+    if (k < Rb::NA) {
+      float c = io.act(k) * Rb::kActScale;
+      // mju_clip(ctrl, lo, hi) = max(lo, min(hi, ctrl)); NaN passes through
+      c = c > Rb::ctrl_hi(k) ? Rb::ctrl_hi(k) : c;
+      c = c < Rb::ctrl_lo(k) ? Rb::ctrl_lo(k) : c;
+      t = Rb::gear(k) * c;
+    }
+    io.tau(k, t);
+  }
+}
+
+// ---- imitation reward (calc_imitation_reward) ---------------------------------------------
+struct RewardMid {
+  float sum_dq, max_dq, d_roll, d_pitch;
+};
+
+template <class Rb, class IO, bool WANT_COM>
+DM_HD float imitation_reward(const IO& io, const FkOut<float>& fk, const float* root_rpy,
+                             const float* __restrict__ row, StepOut& so, RewardMid& mid) {
+  using RL = RowLayout<Rb>;
+  float e_q = 0.0f, e_v = 0.0f, mx = 0.0f;
+  int nlim = 0;
+#pragma unroll
+  for (int k = 0; k < Rb::NSEL; ++k) {
+    const float q = io.qpos(Rb::sel_q(k));
+    const float d = fabsf(q - row[RL::Q + k]);
+    e_q += d;
+    mx = dm_max_nan(mx, d);
+    e_v += fabsf(row[RL::V + k] - io.qvel(Rb::sel_q(k) - 1));
+    nlim += (q <= Rb::lim_lo(k)) + (q >= Rb::lim_hi(k));
+  }
+  const float roll = root_rpy[0], pitch = root_rpy[1];
+  mid.sum_dq = e_q;
+  mid.max_dq = mx;
+  mid.d_roll = fabsf(roll - row[RL::ROLL]);
+  mid.d_pitch = fabsf(pitch - row[RL::PITCH]);
+  const float r_pose = expf(-(e_q + mid.d_pitch));
+  const float r_vel = expf(-0.1f * e_v);
+  float e_ee = 0.0f;
+#pragma unroll
+  for (int k = 0; k < 12; ++k) {
+    const float d = fk.ee[k] - row[RL::EE + k];
+    e_ee = fmaf(d, d, e_ee);
+  }
+  const float r_ee = expf(-40.0f * e_ee);
+  float r_com = 0.0f;
+  if (WANT_COM) {
+    const float dx = row[RL::COM + 0] - fk.com_xpos[0], dy = row[RL::COM + 1] - fk.com_xpos[1],
+                dz = row[RL::COM + 2] - fk.com_xpos[2];
+    r_com = expf(-10.0f * (dx * dx + dy * dy + dz * dz));
+  }
+  const float qlim = float(nlim) / float(Rb::NSEL);
+  so.terms[0] = r_pose;
+  so.terms[1] = r_vel;
+  so.terms[2] = r_ee;
+  so.terms[3] = r_com;
+  so.terms[4] = qlim;
+  // wp 0.75, wv 0.1, we 0.15, wc 0.0, wj -0.1 (deepmimic_env.py:400-404); the wc term is exactly 0
+  return 0.75f * r_pose + 0.1f * r_vel + 0.15f * r_ee + (-0.1f) * qlim;
+}
+
+// ---- one environment step --------------------------------------------------------------------
+template <int KIND, class Rb, class IO, bool WANT_TERMS>
+DM_HD void env_step(IO& io, const ClipSet& cs, EnvState& st, uint32_t contact, StepOut& so) {
+  using RL = RowLayout<Rb>;
+  using OL = ObsLayout<KIND, Rb>;
+  const int clip0 = st.clip;
+  const ClipDesc cd = cs.clip[clip0];
+  const int frame = (KIND == KIND_SINGLE) ? st.idx : (st.idx % cd.len);
+  const int row_i = cd.row0 + (cd.fixed_row >= 0 ? cd.fixed_row : frame);
+  const float* __restrict__ row = cs.rows + size_t(row_i) * RL::STRIDE;
+
+  write_torque<Rb>(io);
+
+  FkOut<float> fk;
+  NullSink sink;
+  Rb::template fk<float>(io, fk, sink);
+
+  float root_rpy[3];
+  dm_rpy_raw(io.qpos(3), io.qpos(4), io.qpos(5), io.qpos(6), root_rpy[0], root_rpy[1], root_rpy[2]);
+  float omax, omin;
+  write_obs<KIND, Rb>(io, fk, root_rpy, contact, frame, cd.len, clip0, omax, omin);
+
+  RewardMid mid;
+  const float imit = imitation_reward<Rb, IO, WANT_TERMS>(io, fk, root_rpy, row, so, mid);
+  const float z = fk.com[2];
+  so.terms[7] = z;
+  bool done = false;
+  int reason = R_NONE;
+  float reward;
+
+  if (KIND == KIND_SINGLE) {
+    reward = imit;
+    so.terms[5] = imit;
+    so.terms[6] = 0.0f;
+    if (!(cd.flags & CLIP_FLOOR)) {  // deepmimic_env.py:420-424 (reason is written even when not done)
+      const bool low = double(z) < double(Rb::kLowZd());
+      done = low || (z > 2.0f);
+      reason = low ? R_LOW_Z : R_HIGH_Z;
+    }
+    if (cd.flags & CLIP_G1_RUN) {  // :426-433
+      if (double(mid.d_roll) > kDeg60) { done = true; reason = R_RUN_ROLL; }
+      if (double(mid.d_pitch) > kDeg60) { done = true; reason = R_RUN_PITCH; }
+    }
+    if (st.ep_len >= OL::MAX_EP) { done = true; reason = R_MAX_EP; }                                    // :435-438
+    if (frame + 1 == cd.len && (cd.flags & CLIP_ACYCLIC)) { done = true; reason = R_ACYC_END; }         // :440-442
+    st.idx = (frame + 1) % cd.len;                                                                      // :452
+    st.ep_len += 1;
+  } else {
+    float task = 0.0f, im = imit;
+    if (clip0 == C_WALK || clip0 == C_RUN) {  // combined_env.py:340-347
+      const float dx = row[RL::VXY + 0] - io.qvel(0), dy = row[RL::VXY + 1] - io.qvel(1);
+      task = expf(-10.0f * sqrtf(dx * dx + dy * dy));
+    }
+    if (clip0 == C_TO_GETUP) {  // :348-352
+      im = 0.0f;
+      task = expf(-(mid.sum_dq + mid.d_pitch + mid.d_roll) / 5.0f) / 3.0f;
+    }
+    reward = im * 0.7f + task * 0.3f;
+    so.terms[5] = im;
+    so.terms[6] = task;
+    int clip = clip0, n = st.idx;
+    if (n >= cd.len - 1) {                       // :399-404
+      if (clip == C_GETUP) { clip = C_RUN; n = 0; }  // Q3: identity comparison -> always the run clip
+      if (clip == C_TO_GETUP) { clip = C_GETUP; n = 0; }
+    }
+    const bool ok = double(mid.d_pitch) < kDeg15 && double(mid.d_roll) < kDeg15 && double(mid.max_dq) < kDeg15;
+    if (ok && clip == C_TO_GETUP) { clip = C_GETUP; n = 0; }  // :418-420
+    if (clip == C_WALK || clip == C_RUN) {                    // :422-440
+      bool fallen = double(z) < double(Rb::kLowZd()) || z > 2.0f;
+      if (double(mid.d_roll) > kDeg60 || double(mid.d_pitch) > kDeg60) fallen = true;
+      if (fallen) {
+        if (!(n > kAmnestySteps)) { done = true; reason = R_FALLEN; }
+        clip = C_TO_GETUP;
+        n = 0;
+      }
+    }
+    if (st.ep_len >= OL::MAX_EP) { done = true; reason = R_MAX_EP; }  // :442-445
+    st.clip = clip;
+    st.idx = n + 1;                                                    // :458-459
+    st.ep_len += 1;
+  }
+  so.reward = reward;
+  so.raw_reward = reward;
+  so.done = done ? 1 : 0;
+  so.reason = uint8_t(reason);
+  // observation bounds guard (deepmimic_env.py:465-476, combined_env.py:474-485): zero observation,
+  // zero reward, done, empty info -- evaluated after the counters advanced
+  if (omax > 100.0f || omin < -100.0f) {
+#pragma unroll 1
+    for (int j = 0; j < OL::DIM; ++j) io.obs(j, 0.0f);
+    so.reward = 0.0f;
+    so.done = 1;
+    so.reason = R_OBS_BOUNDS;
+  }
+}
+
+}  // namespace dm

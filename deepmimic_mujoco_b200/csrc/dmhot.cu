@@ -1,0 +1,510 @@
+// libdmhot.so -- C ABI over the kernels (see include/dmhot.h for the contract and the reference
+// code each entry point replaces).  Host side is plain C++: argument checking, packing of clip
+// tables, launches.  No CPU implementation of the step exists in this library.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/dmhot.h"
+#include "dm_kernels.cuh"
+#include "dm_tile_kernel.cuh"
+#include "dm_pack.h"
+
+using namespace dm;
+
+static thread_local std::string g_last_error;
+
+struct dm_handle {
+  int device = 0, robot = 0, kind = 0;
+  dm_dims_t dims{};
+  std::string err;
+  // clip tables
+  float* d_rows = nullptr;        // packed reward rows [total_rows, row_stride]
+  float* d_state_rows = nullptr;  // [total_rows, nq + nv]
+  std::vector<float> h_rows;
+  int total_rows = 0;
+  ClipSet cs{};
+  // statistics
+  double* d_stats = nullptr;
+  // host-mode staging
+  void* h_pin = nullptr;
+  void* d_stage = nullptr;
+  size_t stage_bytes = 0;
+  cudaStream_t host_stream = nullptr;
+  // bookkeeping
+  long long launches = 0;
+  int variant = -1;  // -1 auto
+  bool timing = false;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev;
+  size_t ev_used = 0;
+  double t_ms = 0;
+  long long t_n = 0;
+};
+
+static int fail(dm_handle* h, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_last_error = buf;
+  if (h) h->err = buf;
+  return code;
+}
+#define CU(h, call)                                                                                  \
+  do {                                                                                               \
+    cudaError_t e_ = (call);                                                                         \
+    if (e_ != cudaSuccess) return fail(h, DM_E_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+
+template <class F>
+static int dispatch(const dm_handle* h, F&& f) {  // robot x env kind -> template instantiation
+  if (h->robot == DM_ROBOT_HUMANOID3D && h->kind == DM_ENV_SINGLE) return f(Robot_humanoid3d{}, std::integral_constant<int, KIND_SINGLE>{});
+  if (h->robot == DM_ROBOT_UNITREE_G1 && h->kind == DM_ENV_SINGLE) return f(Robot_unitree_g1{}, std::integral_constant<int, KIND_SINGLE>{});
+  if (h->robot == DM_ROBOT_UNITREE_G1 && h->kind == DM_ENV_COMBINED) return f(Robot_unitree_g1{}, std::integral_constant<int, KIND_COMBINED>{});
+  return DM_E_ARG;
+}
+
+extern "C" int dm_abi_version(void) { return DM_ABI_VERSION; }
+
+extern "C" const char* dm_last_error(const dm_handle* h) { return h ? h->err.c_str() : g_last_error.c_str(); }
+
+extern "C" int dm_create(int device, int robot, int env_kind, dm_handle** out) {
+  if (!out) return fail(nullptr, DM_E_ARG, "dm_create: out is NULL");
+  *out = nullptr;
+  if (robot != DM_ROBOT_HUMANOID3D && robot != DM_ROBOT_UNITREE_G1) return fail(nullptr, DM_E_ARG, "dm_create: unknown robot %d", robot);
+  if (env_kind != DM_ENV_SINGLE && env_kind != DM_ENV_COMBINED) return fail(nullptr, DM_E_ARG, "dm_create: unknown env kind %d", env_kind);
+  if (env_kind == DM_ENV_COMBINED && robot != DM_ROBOT_UNITREE_G1)
+    return fail(nullptr, DM_E_ARG, "dm_create: DPCombinedEnv exists for unitree_g1 only (combined_env.py:164)");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(nullptr, DM_E_CUDA, "dm_create: no CUDA device (%s); this library has no CPU path", cudaGetErrorString(e));
+  if (device < 0 || device >= ndev) return fail(nullptr, DM_E_ARG, "dm_create: device %d out of range (%d devices)", device, ndev);
+  CU(nullptr, cudaSetDevice(device));
+  dm_handle* h = new dm_handle();
+  h->device = device;
+  h->robot = robot;
+  h->kind = env_kind;
+  dispatch(h, [&](auto rb, auto kind) -> int {
+    using Rb = decltype(rb);
+    using OL = ObsLayout<decltype(kind)::value, Rb>;
+    dm_dims_t& d = h->dims;
+    d.nq = Rb::NQ; d.nv = Rb::NV; d.nu = Rb::NU; d.na = Rb::NA; d.obs_dim = OL::DIM;
+    d.nbody = Rb::NBODY; d.ngeom = Rb::NGEOM; d.nsel = Rb::NSEL; d.row_stride = RowLayout<Rb>::STRIDE;
+    d.n_stats = 6 + 2 * OL::DIM; d.robot = robot; d.env_kind = env_kind;
+    return 0;
+  });
+  if (cudaMalloc(&h->d_stats, sizeof(double) * h->dims.n_stats) != cudaSuccess ||
+      cudaMemset(h->d_stats, 0, sizeof(double) * h->dims.n_stats) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&h->host_stream, cudaStreamNonBlocking) != cudaSuccess) {
+    int rc = fail(nullptr, DM_E_CUDA, "dm_create: %s", cudaGetErrorString(cudaGetLastError()));
+    delete h;
+    return rc;
+  }
+  *out = h;
+  return DM_OK;
+}
+
+extern "C" int dm_destroy(dm_handle* h) {
+  if (!h) return DM_OK;
+  cudaSetDevice(h->device);
+  cudaFree(h->d_rows);
+  cudaFree(h->d_state_rows);
+  cudaFree(h->d_stats);
+  cudaFree(h->d_stage);
+  if (h->h_pin) cudaFreeHost(h->h_pin);
+  for (auto& p : h->ev) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
+  if (h->host_stream) cudaStreamDestroy(h->host_stream);
+  delete h;
+  return DM_OK;
+}
+
+extern "C" int dm_get_dims(const dm_handle* h, dm_dims_t* out) {
+  if (!h || !out) return fail(nullptr, DM_E_ARG, "dm_get_dims: NULL argument");
+  *out = h->dims;
+  return DM_OK;
+}
+
+extern "C" int dm_get_model(const dm_handle* h, double* body_mass, float* lim_lo, float* lim_hi, float* gear, float* ctrl_lo,
+                            float* ctrl_hi, int32_t* ee_geom) {
+  if (!h) return fail(nullptr, DM_E_ARG, "dm_get_model: NULL handle");
+  return dispatch(h, [&](auto rb, auto) -> int {
+    using Rb = decltype(rb);
+    for (int i = 0; i < Rb::NBODY; ++i) if (body_mass) body_mass[i] = Rb::body_mass(i);
+    for (int k = 0; k < Rb::NSEL; ++k) {
+      if (lim_lo) lim_lo[k] = Rb::lim_lo(k);
+      if (lim_hi) lim_hi[k] = Rb::lim_hi(k);
+    }
+    for (int k = 0; k < Rb::NU; ++k) {
+      if (gear) gear[k] = Rb::gear(k);
+      if (ctrl_lo) ctrl_lo[k] = Rb::ctrl_lo(k);
+      if (ctrl_hi) ctrl_hi[k] = Rb::ctrl_hi(k);
+    }
+    for (int k = 0; k < 4; ++k) if (ee_geom) ee_geom[k] = Rb::ee_geom(k);
+    return DM_OK;
+  });
+}
+
+extern "C" int dm_fk_tables(dm_handle* h, int32_t n, const double* qpos, const double* qvel, double* body_xpos, double* geom_xpos) {
+  if (!h || n <= 0 || !qpos || !qvel || !body_xpos || !geom_xpos) return fail(h, DM_E_ARG, "dm_fk_tables: bad argument");
+  CU(h, cudaSetDevice(h->device));
+  const dm_dims_t& d = h->dims;
+  const size_t bq = sizeof(double) * n * d.nq, bv = sizeof(double) * n * d.nv, bb = sizeof(double) * n * d.nbody * 3,
+               bg = sizeof(double) * n * d.ngeom * 3;
+  double *dq = nullptr, *dv = nullptr, *db = nullptr, *dg = nullptr;
+  int rc = DM_OK;
+  auto cleanup = [&] { cudaFree(dq); cudaFree(dv); cudaFree(db); cudaFree(dg); };
+#define CUF(call)                                                                         \
+  do {                                                                                    \
+    cudaError_t e_ = (call);                                                              \
+    if (e_ != cudaSuccess) { rc = fail(h, DM_E_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); cleanup(); return rc; } \
+  } while (0)
+  CUF(cudaMalloc(&dq, bq)); CUF(cudaMalloc(&dv, bv)); CUF(cudaMalloc(&db, bb)); CUF(cudaMalloc(&dg, bg));
+  CUF(cudaMemcpy(dq, qpos, bq, cudaMemcpyHostToDevice));
+  CUF(cudaMemcpy(dv, qvel, bv, cudaMemcpyHostToDevice));
+  dispatch(h, [&](auto rb, auto) -> int {
+    using Rb = decltype(rb);
+    fk_table_kernel<Rb><<<(n + 63) / 64, 64>>>(n, dq, dv, db, dg);
+    return 0;
+  });
+  h->launches++;
+  CUF(cudaGetLastError());
+  CUF(cudaMemcpy(body_xpos, db, bb, cudaMemcpyDeviceToHost));
+  CUF(cudaMemcpy(geom_xpos, dg, bg, cudaMemcpyDeviceToHost));
+#undef CUF
+  cleanup();
+  return DM_OK;
+}
+
+// Packs the reward rows on the host in float64 and uploads them as fp32 (dm_step.cuh: RowLayout).
+extern "C" int dm_upload_clips(dm_handle* h, int32_t n_clips, const dm_clip_t* clips) {
+  if (!h || !clips || n_clips <= 0 || n_clips > DM_MAX_CLIPS) return fail(h, DM_E_ARG, "dm_upload_clips: need 1..%d clips", DM_MAX_CLIPS);
+  if (h->kind == DM_ENV_COMBINED && n_clips != 4)
+    return fail(h, DM_E_ARG, "dm_upload_clips: DPCombinedEnv needs exactly 4 clips (walk, run, getup, to_getup)");
+  CU(h, cudaSetDevice(h->device));
+  return dispatch(h, [&](auto rb, auto) -> int {
+    using Rb = decltype(rb);
+    using RL = RowLayout<Rb>;
+    ClipSet cs{};
+    std::vector<float> rows, srows;
+    int total = 0;
+    const char* bad = pack_clip_rows<Rb>(clips, n_clips, cs, rows, srows, total);
+    if (bad) return fail(h, DM_E_ARG, "dm_upload_clips: %s", bad);
+    cudaFree(h->d_rows);
+    cudaFree(h->d_state_rows);
+    h->d_rows = h->d_state_rows = nullptr;
+    CU(h, cudaMalloc(&h->d_rows, rows.size() * sizeof(float)));
+    CU(h, cudaMalloc(&h->d_state_rows, srows.size() * sizeof(float)));
+    CU(h, cudaMemcpy(h->d_rows, rows.data(), rows.size() * sizeof(float), cudaMemcpyHostToDevice));
+    CU(h, cudaMemcpy(h->d_state_rows, srows.data(), srows.size() * sizeof(float), cudaMemcpyHostToDevice));
+    cs.rows = h->d_rows;
+    h->cs = cs;
+    h->total_rows = total;
+    h->h_rows.swap(rows);
+    return DM_OK;
+  });
+}
+
+extern "C" int dm_get_packed_rows(const dm_handle* h, float* rows, int32_t* total_rows) {
+  if (!h || !total_rows) return fail(nullptr, DM_E_ARG, "dm_get_packed_rows: NULL argument");
+  *total_rows = h->total_rows;
+  if (rows) memcpy(rows, h->h_rows.data(), h->h_rows.size() * sizeof(float));
+  return DM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+static int check_step_args(dm_handle* h, const dm_step_args* a, const char* who) {
+  if (!h || !a) return fail(h, DM_E_ARG, "%s: NULL argument", who);
+  if (!h->d_rows) return fail(h, DM_E_STATE, "%s: no clips uploaded (call dm_upload_clips first)", who);
+  if (a->n < 0) return fail(h, DM_E_ARG, "%s: n = %d", who, a->n);
+  if (a->layout != DM_LAYOUT_AOS && a->layout != DM_LAYOUT_SOA) return fail(h, DM_E_ARG, "%s: unknown layout %d", who, a->layout);
+  if (a->layout == DM_LAYOUT_SOA && a->ld < a->n) return fail(h, DM_E_ARG, "%s: SoA ld %lld < n %d", who, (long long)a->ld, a->n);
+  if (!a->qpos || !a->qvel || !a->action || !a->idx || !a->ep_len || !a->obs || !a->reward || !a->done)
+    return fail(h, DM_E_ARG, "%s: a required buffer is NULL (qpos qvel action idx ep_len obs reward done)", who);
+  if (h->kind == DM_ENV_COMBINED && !a->clip) return fail(h, DM_E_ARG, "%s: DPCombinedEnv needs the clip (motion state) buffer", who);
+  return DM_OK;
+}
+
+static void timing_begin(dm_handle* h, cudaStream_t s) {
+  if (!h->timing) return;
+  if (h->ev_used == h->ev.size()) {
+    cudaEvent_t a, b;
+    cudaEventCreate(&a);
+    cudaEventCreate(&b);
+    h->ev.emplace_back(a, b);
+  }
+  cudaEventRecord(h->ev[h->ev_used].first, s);
+}
+static void timing_end(dm_handle* h, cudaStream_t s) {
+  if (!h->timing) return;
+  cudaEventRecord(h->ev[h->ev_used].second, s);
+  h->ev_used++;
+}
+
+static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
+  if (a->n == 0) return DM_OK;
+  return dispatch(h, [&](auto rb, auto kind) -> int {
+    using Rb = decltype(rb);
+    constexpr int KIND = decltype(kind)::value;
+    StepParams p{};
+    p.n = a->n;
+    p.aos = a->layout == DM_LAYOUT_AOS;
+    p.es = p.aos ? 1 : a->ld;
+    p.qpos = a->qpos; p.qvel = a->qvel; p.action = a->action; p.contact = a->contact;
+    p.idx = a->idx; p.ep_len = a->ep_len; p.clip = a->clip;
+    p.obs = a->obs; p.reward = a->reward; p.done = a->done; p.reason = a->reason;
+    p.torque = a->torque; p.terms = a->terms; p.ep_return = a->ep_return;
+    p.cs = h->cs;
+    const int block = 128;
+    const int grid = (a->n + block - 1) / block;
+    timing_begin(h, s);
+    if (a->terms) step_strided_kernel<KIND, Rb, true><<<grid, block, 0, s>>>(p);
+    else step_strided_kernel<KIND, Rb, false><<<grid, block, 0, s>>>(p);
+    timing_end(h, s);
+    h->launches++;
+    CU(h, cudaGetLastError());
+    if (a->accumulate_stats) {
+      StatsParams sp{a->n, h->dims.obs_dim, p.es, p.aos, a->obs, a->reward, a->done, a->ep_return, a->ep_len, h->d_stats};
+      const int sgrid = (a->n + 2047) / 2048 < 1 ? 1 : (a->n + 2047) / 2048;
+      stats_kernel<<<sgrid > 1184 ? 1184 : sgrid, dim3(32, 8), 0, s>>>(sp);
+      h->launches++;
+      CU(h, cudaGetLastError());
+    }
+    return DM_OK;
+  });
+}
+
+extern "C" int dm_step(dm_handle* h, const dm_step_args* a) {
+  int rc = check_step_args(h, a, "dm_step");
+  if (rc) return rc;
+  CU(h, cudaSetDevice(h->device));
+  return launch_step(h, a, (cudaStream_t)a->stream);
+}
+
+static int launch_reset(dm_handle* h, const dm_reset_args* a, cudaStream_t s) {
+  if (a->n == 0) return DM_OK;
+  return dispatch(h, [&](auto rb, auto kind) -> int {
+    using Rb = decltype(rb);
+    constexpr int KIND = decltype(kind)::value;
+    ResetParams p{};
+    p.n = a->n;
+    p.aos = a->layout == DM_LAYOUT_AOS;
+    p.es = p.aos ? 1 : a->ld;
+    p.mask = a->mask; p.frame = a->frame; p.coin = a->coin; p.contact = a->contact;
+    p.seed = a->seed; p.counter = a->counter;
+    p.qpos = a->qpos; p.qvel = a->qvel; p.idx = a->idx; p.ep_len = a->ep_len; p.clip = a->clip;
+    p.obs = a->obs; p.ep_return = a->ep_return; p.state_rows = h->d_state_rows; p.cs = h->cs;
+    reset_kernel<KIND, Rb><<<(a->n + 127) / 128, 128, 0, s>>>(p);
+    h->launches++;
+    CU(h, cudaGetLastError());
+    return DM_OK;
+  });
+}
+
+static int check_reset_args(dm_handle* h, const dm_reset_args* a, const char* who) {
+  if (!h || !a) return fail(h, DM_E_ARG, "%s: NULL argument", who);
+  if (!h->d_rows) return fail(h, DM_E_STATE, "%s: no clips uploaded", who);
+  if (a->n < 0 || !a->idx || !a->ep_len || !a->obs) return fail(h, DM_E_ARG, "%s: idx / ep_len / obs are required", who);
+  if (a->layout == DM_LAYOUT_SOA && a->ld < a->n) return fail(h, DM_E_ARG, "%s: SoA ld < n", who);
+  if (h->kind == DM_ENV_COMBINED && !a->clip) return fail(h, DM_E_ARG, "%s: DPCombinedEnv needs the clip buffer", who);
+  return DM_OK;
+}
+
+extern "C" int dm_reset(dm_handle* h, const dm_reset_args* a) {
+  int rc = check_reset_args(h, a, "dm_reset");
+  if (rc) return rc;
+  CU(h, cudaSetDevice(h->device));
+  return launch_reset(h, a, (cudaStream_t)a->stream);
+}
+
+// ---- host-buffer variants ---------------------------------------------------------------------
+static int ensure_stage(dm_handle* h, size_t bytes) {
+  if (bytes <= h->stage_bytes) return DM_OK;
+  cudaFree(h->d_stage);
+  if (h->h_pin) cudaFreeHost(h->h_pin);
+  h->d_stage = h->h_pin = nullptr;
+  h->stage_bytes = 0;
+  const size_t cap = bytes + bytes / 4 + 4096;
+  CU(h, cudaMalloc(&h->d_stage, cap));
+  CU(h, cudaMallocHost(&h->h_pin, cap));
+  h->stage_bytes = cap;
+  return DM_OK;
+}
+
+struct Carver {  // lays buffers out back to back (256-byte aligned) in the pinned / device staging areas
+  char* hbase;
+  char* dbase;
+  size_t off = 0;
+  template <class T>
+  void take(size_t count, T** hp, T** dp) {
+    off = (off + 255) & ~size_t(255);
+    if (hp) *hp = (T*)(hbase + off);
+    if (dp) *dp = (T*)(dbase + off);
+    off += count * sizeof(T);
+  }
+};
+
+extern "C" int dm_step_host(dm_handle* h, const dm_step_args* a, int64_t* h2d_bytes, int64_t* d2h_bytes) {
+  int rc = check_step_args(h, a, "dm_step_host");
+  if (rc) return rc;
+  if (a->layout != DM_LAYOUT_AOS) return fail(h, DM_E_ARG, "dm_step_host: host buffers are row-major (AoS) only");
+  CU(h, cudaSetDevice(h->device));
+  const dm_dims_t& d = h->dims;
+  const size_t n = a->n;
+  if (n == 0) return DM_OK;
+  const size_t need = n * (sizeof(float) * (d.nq + d.nv + d.na + d.obs_dim + 1 + d.nu + DM_NTERMS + 1) + 4 * 4 + 2) + 16 * 256;
+  rc = ensure_stage(h, need);
+  if (rc) return rc;
+  Carver c{(char*)h->h_pin, (char*)h->d_stage};
+  cudaStream_t s = h->host_stream;
+  // inputs are contiguous in the staging area: one H2D copy
+  float *hq, *dq, *hv, *dv, *ha, *da, *her, *der;
+  uint32_t *hc, *dc;
+  int32_t *hi, *di, *hl, *dl, *hk, *dk;
+  c.take(n * d.nq, &hq, &dq); c.take(n * d.nv, &hv, &dv); c.take(n * d.na, &ha, &da);
+  c.take(n, &hc, &dc); c.take(n, &hi, &di); c.take(n, &hl, &dl); c.take(n, &hk, &dk); c.take(n, &her, &der);
+  const size_t in_bytes = c.off;
+  memcpy(hq, a->qpos, sizeof(float) * n * d.nq);
+  memcpy(hv, a->qvel, sizeof(float) * n * d.nv);
+  memcpy(ha, a->action, sizeof(float) * n * d.na);
+  if (a->contact) memcpy(hc, a->contact, 4 * n); else memset(hc, 0, 4 * n);
+  memcpy(hi, a->idx, 4 * n);
+  memcpy(hl, a->ep_len, 4 * n);
+  if (a->clip) memcpy(hk, a->clip, 4 * n); else memset(hk, 0, 4 * n);
+  if (a->ep_return) memcpy(her, a->ep_return, 4 * n);
+  CU(h, cudaMemcpyAsync(h->d_stage, h->h_pin, in_bytes, cudaMemcpyHostToDevice, s));
+  // outputs, again contiguous: one D2H copy (plus the state ints living in the input block)
+  c.off = (c.off + 255) & ~size_t(255);
+  const size_t out0 = c.off;
+  float *ho, *dob, *hr, *dr, *ht, *dt, *hm, *dm_;
+  uint8_t *hd, *dd, *hz, *dz;
+  c.take(n * d.obs_dim, &ho, &dob); c.take(n, &hr, &dr); c.take(n * d.nu, &ht, &dt); c.take(n * DM_NTERMS, &hm, &dm_);
+  c.take(n, &hd, &dd); c.take(n, &hz, &dz);
+  const size_t out_bytes = c.off - out0;
+  dm_step_args k = *a;
+  k.qpos = dq; k.qvel = dv; k.action = da; k.contact = dc; k.idx = di; k.ep_len = dl; k.clip = dk;
+  k.obs = dob; k.reward = dr; k.done = dd; k.reason = dz; k.torque = a->torque ? dt : nullptr;
+  k.terms = a->terms ? dm_ : nullptr; k.ep_return = a->ep_return ? der : nullptr;
+  rc = launch_step(h, &k, s);
+  if (rc) return rc;
+  CU(h, cudaMemcpyAsync((char*)h->h_pin + out0, (char*)h->d_stage + out0, out_bytes, cudaMemcpyDeviceToHost, s));
+  const size_t st0 = (char*)hi - (char*)h->h_pin, st_bytes = (char*)(her + n) - (char*)hi;
+  CU(h, cudaMemcpyAsync((char*)h->h_pin + st0, (char*)h->d_stage + st0, st_bytes, cudaMemcpyDeviceToHost, s));
+  CU(h, cudaStreamSynchronize(s));
+  memcpy(a->obs, ho, sizeof(float) * n * d.obs_dim);
+  memcpy(a->reward, hr, 4 * n);
+  memcpy(a->done, hd, n);
+  if (a->reason) memcpy(a->reason, hz, n);
+  if (a->torque) memcpy(a->torque, ht, sizeof(float) * n * d.nu);
+  if (a->terms) memcpy(a->terms, hm, sizeof(float) * n * DM_NTERMS);
+  memcpy(a->idx, hi, 4 * n);
+  memcpy(a->ep_len, hl, 4 * n);
+  if (a->clip) memcpy(a->clip, hk, 4 * n);
+  if (a->ep_return) memcpy(a->ep_return, her, 4 * n);
+  if (h2d_bytes) *h2d_bytes = (int64_t)in_bytes;
+  if (d2h_bytes) *d2h_bytes = (int64_t)(out_bytes + st_bytes);
+  return DM_OK;
+}
+
+extern "C" int dm_reset_host(dm_handle* h, const dm_reset_args* a) {
+  int rc = check_reset_args(h, a, "dm_reset_host");
+  if (rc) return rc;
+  if (a->layout != DM_LAYOUT_AOS) return fail(h, DM_E_ARG, "dm_reset_host: AoS only");
+  CU(h, cudaSetDevice(h->device));
+  const dm_dims_t& d = h->dims;
+  const size_t n = a->n;
+  if (n == 0) return DM_OK;
+  rc = ensure_stage(h, n * (sizeof(float) * (d.nq + d.nv + d.obs_dim + 1) + 4 * 6 + 1) + 16 * 256);
+  if (rc) return rc;
+  Carver c{(char*)h->h_pin, (char*)h->d_stage};
+  cudaStream_t s = h->host_stream;
+  uint8_t *hm, *dmk;
+  int32_t *hf, *df, *hco, *dco, *hi, *di, *hl, *dl, *hk, *dk;
+  uint32_t *hc, *dc;
+  float *hq, *dq, *hv, *dv, *ho, *dob, *her, *der;
+  c.take(n, &hm, &dmk); c.take(n, &hf, &df); c.take(n, &hco, &dco); c.take(n, &hc, &dc);
+  c.take(n, &hi, &di); c.take(n, &hl, &dl); c.take(n, &hk, &dk); c.take(n, &her, &der);
+  c.take(n * d.nq, &hq, &dq); c.take(n * d.nv, &hv, &dv); c.take(n * d.obs_dim, &ho, &dob);
+  if (a->mask) memcpy(hm, a->mask, n); else memset(hm, 1, n);
+  if (a->frame) memcpy(hf, a->frame, 4 * n);
+  if (a->coin) memcpy(hco, a->coin, 4 * n);
+  if (a->contact) memcpy(hc, a->contact, 4 * n); else memset(hc, 0, 4 * n);
+  memcpy(hi, a->idx, 4 * n);
+  memcpy(hl, a->ep_len, 4 * n);
+  if (a->clip) memcpy(hk, a->clip, 4 * n); else memset(hk, 0, 4 * n);
+  if (a->ep_return) memcpy(her, a->ep_return, 4 * n); else memset(her, 0, 4 * n);
+  if (a->qpos) memcpy(hq, a->qpos, sizeof(float) * n * d.nq);
+  if (a->qvel) memcpy(hv, a->qvel, sizeof(float) * n * d.nv);
+  memcpy(ho, a->obs, sizeof(float) * n * d.obs_dim);
+  CU(h, cudaMemcpyAsync(h->d_stage, h->h_pin, c.off, cudaMemcpyHostToDevice, s));
+  dm_reset_args k = *a;
+  k.mask = dmk; k.frame = a->frame ? df : nullptr; k.coin = a->coin ? dco : nullptr; k.contact = dc;
+  k.idx = di; k.ep_len = dl; k.clip = dk; k.ep_return = der; k.qpos = dq; k.qvel = dv; k.obs = dob;
+  rc = launch_reset(h, &k, s);
+  if (rc) return rc;
+  CU(h, cudaMemcpyAsync(h->h_pin, h->d_stage, c.off, cudaMemcpyDeviceToHost, s));
+  CU(h, cudaStreamSynchronize(s));
+  memcpy(a->idx, hi, 4 * n);
+  memcpy(a->ep_len, hl, 4 * n);
+  if (a->clip) memcpy(a->clip, hk, 4 * n);
+  if (a->ep_return) memcpy(a->ep_return, her, 4 * n);
+  if (a->qpos) memcpy(a->qpos, hq, sizeof(float) * n * d.nq);
+  if (a->qvel) memcpy(a->qvel, hv, sizeof(float) * n * d.nv);
+  memcpy(a->obs, ho, sizeof(float) * n * d.obs_dim);
+  return DM_OK;
+}
+
+// ---- statistics, bookkeeping ------------------------------------------------------------------
+extern "C" int dm_stats_zero(dm_handle* h, void* stream) {
+  if (!h) return fail(nullptr, DM_E_ARG, "dm_stats_zero: NULL handle");
+  CU(h, cudaSetDevice(h->device));
+  CU(h, cudaMemsetAsync(h->d_stats, 0, sizeof(double) * h->dims.n_stats, (cudaStream_t)stream));
+  return DM_OK;
+}
+extern "C" int dm_stats_device_ptr(dm_handle* h, double** dev_ptr, int32_t* n) {
+  if (!h || !dev_ptr || !n) return fail(h, DM_E_ARG, "dm_stats_device_ptr: NULL argument");
+  *dev_ptr = h->d_stats;
+  *n = h->dims.n_stats;
+  return DM_OK;
+}
+extern "C" int dm_stats_read(dm_handle* h, double* host_out, void* stream) {
+  if (!h || !host_out) return fail(h, DM_E_ARG, "dm_stats_read: NULL argument");
+  CU(h, cudaSetDevice(h->device));
+  CU(h, cudaMemcpyAsync(host_out, h->d_stats, sizeof(double) * h->dims.n_stats, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  CU(h, cudaStreamSynchronize((cudaStream_t)stream));
+  return DM_OK;
+}
+extern "C" int dm_launch_count(const dm_handle* h, int64_t* kernels) {
+  if (!h || !kernels) return fail(nullptr, DM_E_ARG, "dm_launch_count: NULL argument");
+  *kernels = h->launches;
+  return DM_OK;
+}
+extern "C" int dm_set_timing(dm_handle* h, int enabled) {
+  if (!h) return fail(nullptr, DM_E_ARG, "dm_set_timing: NULL handle");
+  h->timing = enabled != 0;
+  return DM_OK;
+}
+extern "C" int dm_step_kernel_time(dm_handle* h, int reset, double* avg_ms, int64_t* launches) {
+  if (!h) return fail(nullptr, DM_E_ARG, "dm_step_kernel_time: NULL handle");
+  CU(h, cudaSetDevice(h->device));
+  for (size_t i = 0; i < h->ev_used; ++i) {
+    CU(h, cudaEventSynchronize(h->ev[i].second));
+    float ms = 0;
+    CU(h, cudaEventElapsedTime(&ms, h->ev[i].first, h->ev[i].second));
+    h->t_ms += ms;
+    h->t_n++;
+  }
+  h->ev_used = 0;
+  if (avg_ms) *avg_ms = h->t_n ? h->t_ms / h->t_n : 0.0;
+  if (launches) *launches = h->t_n;
+  if (reset) { h->t_ms = 0; h->t_n = 0; }
+  return DM_OK;
+}
+extern "C" int dm_set_kernel_variant(dm_handle* h, int variant) {
+  if (!h || variant < -1 || variant > 1) return fail(h, DM_E_ARG, "dm_set_kernel_variant: variant must be -1, 0 or 1");
+  h->variant = variant;
+  return DM_OK;
+}

@@ -1,0 +1,222 @@
+"""HotPath: Python owner of one libdmhot handle (one robot x env kind on one GPU).
+
+It uploads clip tables and launches the batched step / reset kernels on buffers the caller owns:
+torch CUDA tensors (device pointers + the current torch stream; the resident path) or numpy arrays
+(host pointers; the library stages them through pinned memory -- the end-to-end path).
+There is no CPU implementation behind this class: without libdmhot.so and a CUDA device it raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _native as N
+from . import assets
+from .config import clip_flags
+
+_shared = {}
+
+
+class HotPath:
+    def __init__(self, robot="humanoid3d", combined=False, device=0):
+        self.L = N.lib()
+        self.robot = robot
+        self.combined = bool(combined)
+        self.device = int(device)
+        h = C.c_void_p()
+        N.check(self.L.dm_create(self.device, N.ROBOT_IDS[robot], N.ENV_COMBINED if combined else N.ENV_SINGLE,
+                                 C.byref(h)), None, "dm_create")
+        self.h = h
+        d = N.Dims()
+        N.check(self.L.dm_get_dims(self.h, C.byref(d)), self.h, "dm_get_dims")
+        self.dims = d
+        self.nq, self.nv, self.nu, self.na, self.obs_dim = d.nq, d.nv, d.nu, d.na, d.obs_dim
+        self.clip_names = []
+        self.clip_lens = []
+        self._keep = None
+
+    @classmethod
+    def shared(cls, robot, device=0):
+        """A handle used only for load-time FK (MocapDM)."""
+        key = (robot, device)
+        if key not in _shared:
+            _shared[key] = cls(robot, False, device)
+        return _shared[key]
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.dm_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ model / tables
+    def model_constants(self):
+        d = self.dims
+        out = dict(body_mass=np.zeros(d.nbody), lim_lo=np.zeros(d.nsel, np.float32), lim_hi=np.zeros(d.nsel, np.float32),
+                   gear=np.zeros(d.nu, np.float32), ctrl_lo=np.zeros(d.nu, np.float32), ctrl_hi=np.zeros(d.nu, np.float32),
+                   ee_geom=np.zeros(4, np.int32))
+        N.check(self.L.dm_get_model(self.h, *[N.np_ptr(out[k]) for k in
+                                              ("body_mass", "lim_lo", "lim_hi", "gear", "ctrl_lo", "ctrl_hi", "ee_geom")]),
+                self.h, "dm_get_model")
+        return out
+
+    def fk_tables(self, qpos, qvel):
+        """float64 FK of key frames on the device -> (body_xpos [n,nbody,3], geom_xpos [n,ngeom,3])."""
+        q = np.ascontiguousarray(qpos, dtype=np.float64)
+        v = np.ascontiguousarray(qvel, dtype=np.float64)
+        n = q.shape[0]
+        assert q.shape == (n, self.nq) and v.shape == (n, self.nv)
+        bx = np.zeros((n, self.dims.nbody, 3))
+        gx = np.zeros((n, self.dims.ngeom, 3))
+        N.check(self.L.dm_fk_tables(self.h, n, N.np_ptr(q), N.np_ptr(v), N.np_ptr(bx), N.np_ptr(gx)), self.h, "dm_fk_tables")
+        return bx, gx
+
+    def upload_mocaps(self, mocaps, flags, names=None, transition=None):
+        """mocaps: MocapDM-like objects (data_config / data_vel / data_body_xpos / data_geom_xpos).
+        transition = (target_index, virtual_len, frame): appends a MotionTransition clip."""
+        n = len(mocaps) + (1 if transition else 0)
+        clips = (N.Clip * n)()
+        keep = []
+        for i, m in enumerate(mocaps):
+            arrs = [np.ascontiguousarray(np.asarray(x, dtype=np.float64)) for x in
+                    (m.data_config, m.data_vel, m.data_body_xpos, m.data_geom_xpos)]
+            keep.append(arrs)
+            L = len(arrs[0])
+            clips[i] = N.Clip(L, L, int(flags[i]), -1, *[N.np_ptr(a) for a in arrs])
+        if transition:
+            t, vlen, frame = transition
+            a = keep[t]
+            clips[n - 1] = N.Clip(int(vlen), len(a[0]), 0, int(frame), *[N.np_ptr(x) for x in a])
+        N.check(self.L.dm_upload_clips(self.h, n, clips), self.h, "dm_upload_clips")
+        self.clip_lens = [int(clips[i].len) for i in range(n)]
+        self.clip_names = list(names) if names else ["clip%d" % i for i in range(n)]
+        self._keep = keep
+        return self
+
+    def load_motions(self, motions):
+        """DPEnv semantics: one clip per motion name (per-env clip ids select among them)."""
+        from .mocap import MocapDM
+        mocaps = [MocapDM(self.robot, hotpath=self).load_motion(m) for m in motions]
+        self.mocaps = mocaps
+        return self.upload_mocaps(mocaps, [clip_flags(self.robot, m) for m in motions], list(motions))
+
+    def load_combined(self):
+        """DPCombinedEnv: walk, run, getup_facedown_towalk + MTToGetup (combined_env.py:167-178)."""
+        from .mocap import MocapDM
+        motions = ["walk", "run", "getup_facedown_towalk"]
+        mocaps = [MocapDM(self.robot, hotpath=self).load_motion(m) for m in motions]
+        self.mocaps = mocaps
+        return self.upload_mocaps(mocaps, [0, 0, 0], motions + ["to_getup"], transition=(2, 180, 1))
+
+    def packed_rows(self):
+        n = C.c_int32()
+        N.check(self.L.dm_get_packed_rows(self.h, None, C.byref(n)), self.h, "dm_get_packed_rows")
+        rows = np.zeros((n.value, self.dims.row_stride), np.float32)
+        N.check(self.L.dm_get_packed_rows(self.h, N.np_ptr(rows), C.byref(n)), self.h, "dm_get_packed_rows")
+        return rows
+
+    # ------------------------------------------------------------------ step / reset
+    @staticmethod
+    def _ptr(x):
+        if x is None:
+            return None
+        if isinstance(x, np.ndarray):
+            return x.ctypes.data
+        return x.data_ptr()  # torch tensor
+
+    def _step_args(self, n, qpos, qvel, action, contact, idx, ep_len, clip, obs, reward, done, reason, torque, terms,
+                   ep_return, soa_ld, stats, stream):
+        a = N.StepArgs()
+        a.n = n
+        a.layout = N.LAYOUT_SOA if soa_ld else N.LAYOUT_AOS
+        a.ld = int(soa_ld or 0)
+        for k, v in (("qpos", qpos), ("qvel", qvel), ("action", action), ("contact", contact), ("idx", idx),
+                     ("ep_len", ep_len), ("clip", clip), ("obs", obs), ("reward", reward), ("done", done),
+                     ("reason", reason), ("torque", torque), ("terms", terms), ("ep_return", ep_return)):
+            setattr(a, k, self._ptr(v))
+        a.accumulate_stats = 1 if stats else 0
+        a.stream = stream
+        return a
+
+    def step(self, n, qpos, qvel, action, contact, idx, ep_len, clip, obs, reward, done, reason=None, torque=None,
+             terms=None, ep_return=None, soa_ld=0, stats=False, stream=None):
+        """Device buffers (torch CUDA tensors).  Asynchronous on `stream` (default: torch's current stream)."""
+        if stream is None:
+            import torch
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        a = self._step_args(n, qpos, qvel, action, contact, idx, ep_len, clip, obs, reward, done, reason, torque, terms,
+                            ep_return, soa_ld, stats, stream)
+        N.check(self.L.dm_step(self.h, C.byref(a)), self.h, "dm_step")
+
+    def step_host(self, n, qpos, qvel, action, contact, idx, ep_len, clip, obs, reward, done, reason=None, torque=None,
+                  terms=None, ep_return=None, stats=False):
+        """Host buffers (C-contiguous numpy).  Returns (h2d_bytes, d2h_bytes)."""
+        a = self._step_args(n, qpos, qvel, action, contact, idx, ep_len, clip, obs, reward, done, reason, torque, terms,
+                            ep_return, 0, stats, None)
+        hb, db = C.c_int64(), C.c_int64()
+        N.check(self.L.dm_step_host(self.h, C.byref(a), C.byref(hb), C.byref(db)), self.h, "dm_step_host")
+        return hb.value, db.value
+
+    def _reset_args(self, n, mask, frame, coin, contact, qpos, qvel, idx, ep_len, clip, obs, ep_return, soa_ld, seed,
+                    counter, stream):
+        a = N.ResetArgs()
+        a.n = n
+        a.layout = N.LAYOUT_SOA if soa_ld else N.LAYOUT_AOS
+        a.ld = int(soa_ld or 0)
+        for k, v in (("mask", mask), ("frame", frame), ("coin", coin), ("contact", contact), ("qpos", qpos),
+                     ("qvel", qvel), ("idx", idx), ("ep_len", ep_len), ("clip", clip), ("obs", obs),
+                     ("ep_return", ep_return)):
+            setattr(a, k, self._ptr(v))
+        a.seed, a.counter, a.stream = int(seed), int(counter), stream
+        return a
+
+    def reset(self, n, idx, ep_len, clip, obs, mask=None, frame=None, coin=None, contact=None, qpos=None, qvel=None,
+              ep_return=None, soa_ld=0, seed=0, counter=0, stream=None):
+        if stream is None:
+            import torch
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        a = self._reset_args(n, mask, frame, coin, contact, qpos, qvel, idx, ep_len, clip, obs, ep_return, soa_ld, seed,
+                             counter, stream)
+        N.check(self.L.dm_reset(self.h, C.byref(a)), self.h, "dm_reset")
+
+    def reset_host(self, n, idx, ep_len, clip, obs, mask=None, frame=None, coin=None, contact=None, qpos=None, qvel=None,
+                   ep_return=None, seed=0, counter=0):
+        a = self._reset_args(n, mask, frame, coin, contact, qpos, qvel, idx, ep_len, clip, obs, ep_return, 0, seed,
+                             counter, None)
+        N.check(self.L.dm_reset_host(self.h, C.byref(a)), self.h, "dm_reset_host")
+
+    # ------------------------------------------------------------------ statistics / bookkeeping
+    def stats_zero(self, stream=None):
+        N.check(self.L.dm_stats_zero(self.h, stream), self.h, "dm_stats_zero")
+
+    def stats_read(self, stream=None):
+        out = np.zeros(self.dims.n_stats)
+        N.check(self.L.dm_stats_read(self.h, N.np_ptr(out), stream), self.h, "dm_stats_read")
+        return out
+
+    def stats_device_ptr(self):
+        p, n = C.c_void_p(), C.c_int32()
+        N.check(self.L.dm_stats_device_ptr(self.h, C.byref(p), C.byref(n)), self.h, "dm_stats_device_ptr")
+        return p.value, n.value
+
+    def launch_count(self):
+        k = C.c_int64()
+        N.check(self.L.dm_launch_count(self.h, C.byref(k)), self.h, "dm_launch_count")
+        return k.value
+
+    def set_timing(self, on):
+        N.check(self.L.dm_set_timing(self.h, 1 if on else 0), self.h, "dm_set_timing")
+
+    def kernel_time(self, reset=True):
+        ms, n = C.c_double(), C.c_int64()
+        N.check(self.L.dm_step_kernel_time(self.h, 1 if reset else 0, C.byref(ms), C.byref(n)), self.h, "dm_step_kernel_time")
+        return ms.value, n.value
+
+    def set_kernel_variant(self, v):
+        N.check(self.L.dm_set_kernel_variant(self.h, int(v)), self.h, "dm_set_kernel_variant")

@@ -1,0 +1,175 @@
+/* dmhot -- C ABI of the B200 batched DeepMimic environment hot path (libdmhot.so).
+ *
+ * The reference (danieldugas/DeepMimic_mujoco) is pure Python and has no FFI layer; the boundary
+ * this library sits behind is its gym / VecEnv API.  Each entry point below names the reference
+ * code it replaces (paths relative to the reference root).  INTEGRATION.md shows the ctypes stub a
+ * maintainer would add to src/deepmimic_env.py / src/combined_env.py.
+ *
+ * Conventions: every function returns 0 on success and a negative DM_E_* code on failure, never
+ * throws, never allocates caller-visible memory.  dm_last_error() returns a message for the last
+ * failure on that handle (or the last global failure for handle == NULL).  All `const float*` /
+ * `float*` step buffers are DEVICE pointers owned by the caller (PyTorch); calls are asynchronous
+ * on the given CUDA stream (a cudaStream_t passed as void*).  The *_host variants take HOST
+ * pointers, stage through pinned memory owned by the handle and return after the results are on
+ * the host.  A handle belongs to one device and is not thread-safe.
+ */
+#ifndef DMHOT_H_
+#define DMHOT_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DM_ABI_VERSION 1
+
+enum { DM_ROBOT_HUMANOID3D = 0, DM_ROBOT_UNITREE_G1 = 1 }; /* src/config.py:3-22 RobotConfig */
+enum { DM_ENV_SINGLE = 0,     /* DPEnv          src/deepmimic_env.py:273-510 */
+       DM_ENV_COMBINED = 1 }; /* DPCombinedEnv  src/combined_env.py:102-533 (unitree_g1 only) */
+enum { DM_LAYOUT_AOS = 0,     /* row-major [n, dim]: what gym / SB3 hand over */
+       DM_LAYOUT_SOA = 1 };   /* [dim, ld] with ld >= n: one coalesced column per quantity */
+
+enum { DM_CLIP_FLOOR = 1,   /* motion in MotionConfig.floor_motions      src/config.py:37 */
+       DM_CLIP_ACYCLIC = 2, /* motion in MotionConfig.acyclical_motions  src/config.py:36 */
+       DM_CLIP_G1_RUN = 4 };/* "run" on unitree_g1: roll/pitch limit     src/deepmimic_env.py:426-433 */
+
+/* done_reason codes (info["done_reason"], src/deepmimic_env.py:424-442, src/combined_env.py:436,445);
+ * 8 = observation-bounds guard (returns obs*0, 0, True, {} -- src/deepmimic_env.py:465-476) */
+enum { DM_REASON_NONE = 0, DM_REASON_LOW_Z, DM_REASON_HIGH_Z, DM_REASON_RUN_ROLL, DM_REASON_RUN_PITCH,
+       DM_REASON_MAX_EP_LEN, DM_REASON_ACYCLICAL_END, DM_REASON_FALLEN_NO_AMNESTY, DM_REASON_OBS_BOUNDS };
+
+enum { DM_OK = 0, DM_E_ARG = -1, DM_E_CUDA = -2, DM_E_STATE = -3, DM_E_NOMEM = -4 };
+
+#define DM_MAX_CLIPS 8
+#define DM_NTERMS 8 /* reward_config, reward_qvel, reward_end_eff, reward_com, reward_joint_limit,
+                       imitation_reward, task_reward, z_com */
+/* contact word: bit 0 rfoot&floor, bit 1 lfoot&floor (get_foot_contact_obs, deepmimic_env.py:78-105),
+ * bits 2..9 the eight extra-contact geoms & floor (get_extra_contact_obs, :107-121) */
+
+typedef struct dm_handle dm_handle;
+
+typedef struct {
+  int32_t nq, nv, nu, na;      /* na = exposed action dims (nu - 14 hand motors on G1) */
+  int32_t obs_dim;             /* 67 / 85 / 98 */
+  int32_t nbody, ngeom, nsel;  /* nsel = joints in the reward (deepmimic_env.py:206-207) */
+  int32_t row_stride;          /* floats per packed clip row */
+  int32_t n_stats;             /* doubles in the statistics vector: 6 + 2 * obs_dim */
+  int32_t robot, env_kind;
+} dm_dims_t;
+
+/* One mocap clip = the tables MocapDM.read_raw_data builds (src/mujoco/mocap_v2.py:33-336), float64,
+ * row-major, HOST pointers.  fixed_row >= 0 makes it a MotionTransition (src/combined_env.py:67-99:
+ * every lookup returns that frame, `len` is its virtual length). */
+typedef struct {
+  int32_t len;            /* get_length() */
+  int32_t n_rows;         /* frames actually present in the arrays below (== len unless fixed_row >= 0) */
+  int32_t flags;          /* DM_CLIP_* */
+  int32_t fixed_row;      /* -1, or the constant frame (1 for MTToGetup) */
+  const double* qpos;      /* [n_rows, nq]         data_config    */
+  const double* qvel;      /* [n_rows, nv]         data_vel       */
+  const double* body_xpos; /* [n_rows, nbody, 3]   data_body_xpos */
+  const double* geom_xpos; /* [n_rows, ngeom, 3]   data_geom_xpos */
+} dm_clip_t;
+
+/* Per-step buffers.  For DM_ENV_SINGLE `idx` is idx_curr and `clip` selects the clip of each env
+ * (NULL = clip 0 for all); for DM_ENV_COMBINED `idx` is current_motion_n_steps and `clip` the motion
+ * state (0 walk, 1 run, 2 getup, 3 to_getup).  idx / ep_len / clip are updated in place. */
+typedef struct {
+  int32_t n;
+  int32_t layout;           /* DM_LAYOUT_* for every float buffer */
+  int64_t ld;               /* SoA leading dimension (ignored for AoS) */
+  const float* qpos;        /* [n, nq]  state after the physics step (force_state semantics) */
+  const float* qvel;        /* [n, nv] */
+  const float* action;      /* [n, na] */
+  const uint32_t* contact;  /* [n] contact word, NULL = no contacts */
+  int32_t* idx;             /* [n] in/out */
+  int32_t* ep_len;          /* [n] in/out episode_length */
+  int32_t* clip;            /* [n] in (single) / in-out (combined); may be NULL for single */
+  float* obs;               /* [n, obs_dim] */
+  float* reward;            /* [n] */
+  uint8_t* done;            /* [n] */
+  uint8_t* reason;          /* [n] DM_REASON_*; may be NULL */
+  float* torque;            /* [n, nu] gear * clip(scale * action, ctrlrange); may be NULL */
+  float* terms;             /* [n, DM_NTERMS]; may be NULL */
+  float* ep_return;         /* [n] in/out episode_reward accumulator; may be NULL */
+  int32_t accumulate_stats; /* != 0: add this batch to the handle's statistics accumulators */
+  void* stream;             /* cudaStream_t */
+} dm_step_args;
+
+/* Reset (DPEnv.reset / reset_model / reference_state_init, src/deepmimic_env.py:312-316,496-510;
+ * DPCombinedEnv.reset, src/combined_env.py:208-244) of the envs whose mask byte is non-zero.
+ * frame: injected random.randint draw (NULL = counter-based device RNG from seed/counter).
+ * coin : combined only -- 0 walk (+150+10 amnesty offset), 1 getup, 2 = rsi=False (getup, n_steps 0);
+ *        NULL = device RNG coin flip.  qpos/qvel receive the reference frame (set_state). */
+typedef struct {
+  int32_t n;
+  int32_t layout;
+  int64_t ld;
+  const uint8_t* mask;     /* [n] or NULL = all */
+  const int32_t* frame;    /* [n] or NULL */
+  const int32_t* coin;     /* [n] or NULL */
+  const uint32_t* contact; /* [n] contacts at the reset pose, NULL = none */
+  uint64_t seed, counter;
+  float* qpos;             /* [n, nq] out */
+  float* qvel;             /* [n, nv] out */
+  int32_t* idx;            /* [n] out */
+  int32_t* ep_len;         /* [n] out (0) */
+  int32_t* clip;           /* [n] in (single, may be NULL) / out (combined) */
+  float* obs;              /* [n, obs_dim] out (rows of reset envs only) */
+  float* ep_return;        /* [n] out (0), may be NULL */
+  void* stream;
+} dm_reset_args;
+
+/* lifetime */
+int dm_abi_version(void);
+int dm_create(int device, int robot, int env_kind, dm_handle** out);
+int dm_destroy(dm_handle* h);
+const char* dm_last_error(const dm_handle* h);
+int dm_get_dims(const dm_handle* h, dm_dims_t* out);
+
+/* baked model constants (what MuJoCo's compiled model exposes: model.body_mass, model.jnt_range,
+ * actuator gear / ctrlrange) -- lets the host check them against its own MJCF compilation */
+int dm_get_model(const dm_handle* h, double* body_mass /*[nbody]*/, float* lim_lo /*[nsel]*/, float* lim_hi /*[nsel]*/,
+                 float* gear /*[nu]*/, float* ctrl_lo /*[nu]*/, float* ctrl_hi /*[nu]*/, int32_t* ee_geom /*[4]*/);
+
+/* FK of n key frames in float64 on the device: the load-time stage of MocapDM.read_raw_data
+ * (src/mujoco/mocap_v2.py:292-307: set_state per frame, harvest body_xpos / geom_xpos).  HOST pointers. */
+int dm_fk_tables(dm_handle* h, int32_t n, const double* qpos, const double* qvel, double* body_xpos, double* geom_xpos);
+
+/* pack + upload the clip tables (replaces the per-process MocapDM objects a step indexes:
+ * mocap.get_qpos/get_qvel/get_geom_xpos/get_body_xpos, src/mujoco/mocap_v2.py:338-348) */
+int dm_upload_clips(dm_handle* h, int32_t n_clips, const dm_clip_t* clips);
+/* read back the packed fp32 rows (host, [total_rows, row_stride]); rows == NULL just returns the count */
+int dm_get_packed_rows(const dm_handle* h, float* rows, int32_t* total_rows);
+
+/* the hot path: get_obs + calc_imitation_reward + termination / motion state machine + counters +
+ * obs-bounds guard + action -> torque for n environments (DPEnv.step src/deepmimic_env.py:335-484,
+ * DPCombinedEnv.step src/combined_env.py:246-493, with force_state semantics :355-357) */
+int dm_step(dm_handle* h, const dm_step_args* a);
+int dm_reset(dm_handle* h, const dm_reset_args* a);
+
+/* same, HOST pointers, AoS only: H2D copies, kernel, D2H copies, stream sync.  h2d/d2h (may be NULL)
+ * receive the bytes moved. */
+int dm_step_host(dm_handle* h, const dm_step_args* a, int64_t* h2d_bytes, int64_t* d2h_bytes);
+int dm_reset_host(dm_handle* h, const dm_reset_args* a);
+
+/* reward / observation-normaliser statistics (new functionality, no reference counterpart):
+ * [count, sum r, sum r^2, n_done, sum ep_return(done), sum ep_len(done), sum obs[D], sum obs^2[D]] */
+int dm_stats_zero(dm_handle* h, void* stream);
+int dm_stats_device_ptr(dm_handle* h, double** dev_ptr, int32_t* n); /* for an in-place NCCL all-reduce */
+int dm_stats_read(dm_handle* h, double* host_out, void* stream);
+
+/* launch bookkeeping for bench.py ("gpu_launches") */
+int dm_launch_count(const dm_handle* h, int64_t* kernels);
+/* name + average device time (CUDA events on the launch stream) of the step kernel since the last call
+ * with reset != 0; used for the roofline line */
+int dm_step_kernel_time(dm_handle* h, int reset, double* avg_ms, int64_t* launches);
+int dm_set_timing(dm_handle* h, int enabled);
+/* 0 = generic strided kernel, 1 = shared-memory tile kernel with TMA bulk copies (AoS only); default auto */
+int dm_set_kernel_variant(dm_handle* h, int variant);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DMHOT_H_ */
