@@ -46,7 +46,8 @@ class ResetArgs(C.Structure):
                 ("mask", C.c_void_p), ("frame", C.c_void_p), ("coin", C.c_void_p), ("contact", C.c_void_p),
                 ("seed", C.c_uint64), ("counter", C.c_uint64),
                 ("qpos", C.c_void_p), ("qvel", C.c_void_p), ("idx", C.c_void_p), ("ep_len", C.c_void_p),
-                ("clip", C.c_void_p), ("obs", C.c_void_p), ("ep_return", C.c_void_p), ("stream", C.c_void_p)]
+                ("clip", C.c_void_p), ("obs", C.c_void_p), ("ep_return", C.c_void_p), ("terminal_obs", C.c_void_p),
+                ("stream", C.c_void_p)]
 
 
 # every symbol include/dmhot.h declares (tests check that the library exports each one)

@@ -155,6 +155,7 @@ struct ResetParams {
   int* clip;
   float* obs;
   float* ep_return;
+  float* terminal_obs;
   const float* state_rows;  // [total_rows, NQ + NV] fp32 data_config | data_vel
   ClipSet cs;
 };
@@ -217,6 +218,10 @@ __global__ void __launch_bounds__(128) reset_kernel(const __grid_constant__ Rese
     for (int j = 0; j < Rb::NV; ++j) v[j * p.es] = row[Rb::NQ + j];
   }
   ResetIO io{row, p.obs + (p.aos ? e * OL::DIM : e), p.es, Rb::NQ};
+  if (p.terminal_obs) {
+    float* t = p.terminal_obs + (p.aos ? e * OL::DIM : e);
+    for (int j = 0; j < OL::DIM; ++j) t[j * p.es] = io.ob[j * p.es];
+  }
   FkOut<float> fk;
   NullSink sink;
   Rb::template fk<float>(io, fk, sink);

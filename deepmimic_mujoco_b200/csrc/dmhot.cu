@@ -296,7 +296,7 @@ static int launch_reset(dm_handle* h, const dm_reset_args* a, cudaStream_t s) {
     p.mask = a->mask; p.frame = a->frame; p.coin = a->coin; p.contact = a->contact;
     p.seed = a->seed; p.counter = a->counter;
     p.qpos = a->qpos; p.qvel = a->qvel; p.idx = a->idx; p.ep_len = a->ep_len; p.clip = a->clip;
-    p.obs = a->obs; p.ep_return = a->ep_return; p.state_rows = h->d_state_rows; p.cs = h->cs;
+    p.obs = a->obs; p.ep_return = a->ep_return; p.terminal_obs = a->terminal_obs; p.state_rows = h->d_state_rows; p.cs = h->cs;
     reset_kernel<KIND, Rb><<<(a->n + 127) / 128, 128, 0, s>>>(p);
     h->launches++;
     CU(h, cudaGetLastError());
@@ -417,17 +417,19 @@ extern "C" int dm_reset_host(dm_handle* h, const dm_reset_args* a) {
   const dm_dims_t& d = h->dims;
   const size_t n = a->n;
   if (n == 0) return DM_OK;
-  rc = ensure_stage(h, n * (sizeof(float) * (d.nq + d.nv + d.obs_dim + 1) + 4 * 6 + 1) + 16 * 256);
+  rc = ensure_stage(h, n * (sizeof(float) * (d.nq + d.nv + 2 * d.obs_dim + 1) + 4 * 6 + 1) + 16 * 256);
   if (rc) return rc;
   Carver c{(char*)h->h_pin, (char*)h->d_stage};
   cudaStream_t s = h->host_stream;
   uint8_t *hm, *dmk;
   int32_t *hf, *df, *hco, *dco, *hi, *di, *hl, *dl, *hk, *dk;
   uint32_t *hc, *dc;
-  float *hq, *dq, *hv, *dv, *ho, *dob, *her, *der;
+  float *hq, *dq, *hv, *dv, *ho, *dob, *her, *der, *hto, *dto;
   c.take(n, &hm, &dmk); c.take(n, &hf, &df); c.take(n, &hco, &dco); c.take(n, &hc, &dc);
   c.take(n, &hi, &di); c.take(n, &hl, &dl); c.take(n, &hk, &dk); c.take(n, &her, &der);
   c.take(n * d.nq, &hq, &dq); c.take(n * d.nv, &hv, &dv); c.take(n * d.obs_dim, &ho, &dob);
+  c.take(n * d.obs_dim, &hto, &dto);
+  if (a->terminal_obs) memcpy(hto, a->terminal_obs, sizeof(float) * n * d.obs_dim);
   if (a->mask) memcpy(hm, a->mask, n); else memset(hm, 1, n);
   if (a->frame) memcpy(hf, a->frame, 4 * n);
   if (a->coin) memcpy(hco, a->coin, 4 * n);
@@ -442,7 +444,7 @@ extern "C" int dm_reset_host(dm_handle* h, const dm_reset_args* a) {
   CU(h, cudaMemcpyAsync(h->d_stage, h->h_pin, c.off, cudaMemcpyHostToDevice, s));
   dm_reset_args k = *a;
   k.mask = dmk; k.frame = a->frame ? df : nullptr; k.coin = a->coin ? dco : nullptr; k.contact = dc;
-  k.idx = di; k.ep_len = dl; k.clip = dk; k.ep_return = der; k.qpos = dq; k.qvel = dv; k.obs = dob;
+  k.idx = di; k.ep_len = dl; k.clip = dk; k.ep_return = der; k.qpos = dq; k.qvel = dv; k.obs = dob; k.terminal_obs = a->terminal_obs ? dto : nullptr;
   rc = launch_reset(h, &k, s);
   if (rc) return rc;
   CU(h, cudaMemcpyAsync(h->h_pin, h->d_stage, c.off, cudaMemcpyDeviceToHost, s));
@@ -454,6 +456,7 @@ extern "C" int dm_reset_host(dm_handle* h, const dm_reset_args* a) {
   if (a->qpos) memcpy(a->qpos, hq, sizeof(float) * n * d.nq);
   if (a->qvel) memcpy(a->qvel, hv, sizeof(float) * n * d.nv);
   memcpy(a->obs, ho, sizeof(float) * n * d.obs_dim);
+  if (a->terminal_obs) memcpy(a->terminal_obs, hto, sizeof(float) * n * d.obs_dim);
   return DM_OK;
 }
 

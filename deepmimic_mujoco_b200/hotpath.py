@@ -164,31 +164,31 @@ class HotPath:
         return hb.value, db.value
 
     def _reset_args(self, n, mask, frame, coin, contact, qpos, qvel, idx, ep_len, clip, obs, ep_return, soa_ld, seed,
-                    counter, stream):
+                    counter, stream, terminal_obs=None):
         a = N.ResetArgs()
         a.n = n
         a.layout = N.LAYOUT_SOA if soa_ld else N.LAYOUT_AOS
         a.ld = int(soa_ld or 0)
         for k, v in (("mask", mask), ("frame", frame), ("coin", coin), ("contact", contact), ("qpos", qpos),
                      ("qvel", qvel), ("idx", idx), ("ep_len", ep_len), ("clip", clip), ("obs", obs),
-                     ("ep_return", ep_return)):
+                     ("ep_return", ep_return), ("terminal_obs", terminal_obs)):
             setattr(a, k, self._ptr(v))
         a.seed, a.counter, a.stream = int(seed), int(counter), stream
         return a
 
     def reset(self, n, idx, ep_len, clip, obs, mask=None, frame=None, coin=None, contact=None, qpos=None, qvel=None,
-              ep_return=None, soa_ld=0, seed=0, counter=0, stream=None):
+              ep_return=None, soa_ld=0, seed=0, counter=0, stream=None, terminal_obs=None):
         if stream is None:
             import torch
             stream = torch.cuda.current_stream(self.device).cuda_stream
         a = self._reset_args(n, mask, frame, coin, contact, qpos, qvel, idx, ep_len, clip, obs, ep_return, soa_ld, seed,
-                             counter, stream)
+                             counter, stream, terminal_obs)
         N.check(self.L.dm_reset(self.h, C.byref(a)), self.h, "dm_reset")
 
     def reset_host(self, n, idx, ep_len, clip, obs, mask=None, frame=None, coin=None, contact=None, qpos=None, qvel=None,
-                   ep_return=None, seed=0, counter=0):
+                   ep_return=None, seed=0, counter=0, terminal_obs=None):
         a = self._reset_args(n, mask, frame, coin, contact, qpos, qvel, idx, ep_len, clip, obs, ep_return, 0, seed,
-                             counter, None)
+                             counter, None, terminal_obs)
         N.check(self.L.dm_reset_host(self.h, C.byref(a)), self.h, "dm_reset_host")
 
     # ------------------------------------------------------------------ statistics / bookkeeping

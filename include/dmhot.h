@@ -118,6 +118,8 @@ typedef struct {
   int32_t* clip;           /* [n] in (single, may be NULL) / out (combined) */
   float* obs;              /* [n, obs_dim] out (rows of reset envs only) */
   float* ep_return;        /* [n] out (0), may be NULL */
+  float* terminal_obs;     /* [n, obs_dim] or NULL: rows of reset envs receive the obs they had before the reset
+                              (SB3 VecEnv infos[i]["terminal_observation"]) */
   void* stream;
 } dm_reset_args;
 
