@@ -1,0 +1,215 @@
+"""DPVecEnv: N DeepMimic environments per call behind the Stable-Baselines3 VecEnv surface.
+
+Replaces `SubprocVecEnv([lambda: DPEnv(...)] * N)` / `SubprocVecEnv([DPCombinedEnv] * N)`
+(reference src/sb3_ppo.py:275-278, src/sac_sb3.py:77, src/ppo.py:32, src/profile_subproc_dpenv.py:10):
+`reset() -> obs[N, D]`, `step_async(actions)`, `step_wait() -> (obs, rews, dones, infos)`, with SB3's
+auto-reset convention (a done env returns its reset observation and
+`infos[i]["terminal_observation"]` holds the last one).
+
+MuJoCo's mj_step is outside this package.  Each step therefore needs the post-physics state:
+either `step(actions, force_state=(qpos[N,nq], qvel[N,nv]))` -- the reference's own test hook
+(src/deepmimic_env.py:355-357) -- or a `physics` callback given at construction,
+`physics(qpos, qvel, torque) -> (qpos, qvel, contact_bits)`, which is where a batched simulator plugs in.
+
+Two data paths:
+  host   numpy in / numpy out through `dm_step_host` (pinned staging, H2D + kernel + D2H per step);
+  device `step_tensors(...)` on torch CUDA tensors, no host synchronisation (the resident path).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import _native as N
+from .hotpath import HotPath
+
+
+class Box:
+    """Minimal gym.spaces.Box stand-in (gym is not a dependency)."""
+
+    def __init__(self, low, high, dtype=np.float32):
+        self.low = np.asarray(low, dtype=dtype)
+        self.high = np.asarray(high, dtype=dtype)
+        self.shape = self.low.shape
+        self.dtype = np.dtype(dtype)
+        self._rng = np.random.default_rng(0)
+
+    def seed(self, seed=None):
+        self._rng = np.random.default_rng(seed)
+
+    def sample(self):
+        lo = np.where(np.isfinite(self.low), self.low, -1.0)
+        hi = np.where(np.isfinite(self.high), self.high, 1.0)
+        return self._rng.uniform(lo, hi).astype(self.dtype)
+
+    def contains(self, x):
+        x = np.asarray(x)
+        return x.shape == self.shape and bool(np.all(x >= self.low) and np.all(x <= self.high))
+
+
+class DPVecEnv:
+    def __init__(self, num_envs, motion="walk", robot="humanoid3d", combined=False, device=0, seed=0, physics=None,
+                 info_terms=False):
+        self.num_envs = int(num_envs)
+        self.robot = "unitree_g1" if combined else robot
+        self.combined = bool(combined)
+        self.device = device
+        self.physics = physics
+        self.info_terms = info_terms
+        self.hp = HotPath(self.robot, combined=self.combined, device=device)
+        if self.combined:
+            self.hp.load_combined()
+            self.motions = list(self.hp.clip_names)
+        else:
+            self.motions = [motion] if isinstance(motion, str) else list(motion)
+            self.hp.load_motions(self.motions)
+        d = self.hp.dims
+        mc = self.hp.model_constants()
+        lo, hi = mc["ctrl_lo"][:d.na].copy(), mc["ctrl_hi"][:d.na].copy()
+        if self.combined:  # combined_env.py:194-200: ctrlrange / ACT_SCALE
+            lo, hi = lo / 20.0, hi / 20.0
+        self.action_space = Box(lo, hi)
+        self.observation_space = Box(np.full(d.obs_dim, -np.inf), np.full(d.obs_dim, np.inf))
+        n = self.num_envs
+        self._seed, self._counter = int(seed), 0
+        # host-side per-env state (the reference keeps these as Python attributes of each env)
+        self.idx = np.zeros(n, np.int32)       # idx_curr / current_motion_n_steps
+        self.ep_len = np.zeros(n, np.int32)    # episode_length
+        self.clip = np.zeros(n, np.int32)      # clip id / motion state
+        self.ep_return = np.zeros(n, np.float32)
+        self.qpos = np.zeros((n, d.nq), np.float32)
+        self.qvel = np.zeros((n, d.nv), np.float32)
+        self.obs = np.zeros((n, d.obs_dim), np.float32)
+        self.reward = np.zeros(n, np.float32)
+        self.done = np.zeros(n, np.uint8)
+        self.reason = np.zeros(n, np.uint8)
+        self.torque = np.zeros((n, d.nu), np.float32)
+        self.terms = np.zeros((n, N.NTERMS), np.float32) if info_terms else None
+        self.terminal_obs = np.zeros((n, d.obs_dim), np.float32)
+        self._actions = None
+        self._force = None
+        self.h2d_bytes = self.d2h_bytes = 0
+        self._dev = None
+
+    # ------------------------------------------------------------------ VecEnv surface
+    def set_clips(self, clip_ids):
+        """DPEnv semantics with several motions: which clip each env imitates."""
+        self.clip[:] = np.asarray(clip_ids, dtype=np.int32)
+
+    def seed(self, seed=None):
+        self._seed = int(seed or 0)
+        return [self._seed + i for i in range(self.num_envs)]
+
+    def reset(self, frame=None, coin=None, mask=None):
+        """All envs (or those in `mask`): reference-state initialisation + reset observation."""
+        self._counter += 1
+        self.hp.reset_host(self.num_envs, self.idx, self.ep_len, self.clip, self.obs,
+                           mask=None if mask is None else np.ascontiguousarray(mask, dtype=np.uint8),
+                           frame=None if frame is None else np.ascontiguousarray(frame, dtype=np.int32),
+                           coin=None if coin is None else np.ascontiguousarray(coin, dtype=np.int32),
+                           qpos=self.qpos, qvel=self.qvel, ep_return=self.ep_return, seed=self._seed, counter=self._counter)
+        return self.obs.copy()
+
+    def step_async(self, actions, force_state=None):
+        self._actions = np.ascontiguousarray(actions, dtype=np.float32)
+        assert self._actions.shape == (self.num_envs, self.hp.na), "actions must be [num_envs, %d]" % self.hp.na
+        self._force = force_state
+
+    def step_wait(self):
+        n = self.num_envs
+        contact = None
+        if self._force is not None:
+            qpos = np.ascontiguousarray(self._force[0], dtype=np.float32)
+            qvel = np.ascontiguousarray(self._force[1], dtype=np.float32)
+            if len(self._force) > 2 and self._force[2] is not None:
+                contact = np.ascontiguousarray(self._force[2], dtype=np.uint32)
+        elif self.physics is not None:
+            # torque of the previous action is not known before the kernel ran: compute it on the host the way
+            # MuJoCo would (gear * clip(scale * a, ctrlrange)) is the kernel's job, so physics gets the action
+            qpos, qvel, contact = self.physics(self.qpos, self.qvel, self._actions)
+            qpos = np.ascontiguousarray(qpos, dtype=np.float32)
+            qvel = np.ascontiguousarray(qvel, dtype=np.float32)
+            contact = None if contact is None else np.ascontiguousarray(contact, dtype=np.uint32)
+        else:
+            raise N.DmError("DPVecEnv.step needs force_state=(qpos, qvel[, contact]) or a physics callback: MuJoCo's "
+                            "mj_step is outside this package")
+        assert qpos.shape == self.qpos.shape and qvel.shape == self.qvel.shape
+        self.qpos, self.qvel = qpos.copy(), qvel.copy()
+        h2d, d2h = self.hp.step_host(n, self.qpos, self.qvel, self._actions, contact, self.idx, self.ep_len, self.clip,
+                                     self.obs, self.reward, self.done, self.reason, self.torque, self.terms, self.ep_return)
+        self.h2d_bytes, self.d2h_bytes = h2d, d2h
+        dones = self.done.astype(bool)
+        rews = self.reward.copy()
+        infos = [{} for _ in range(n)]
+        if self.info_terms:
+            for i in range(n):
+                if self.reason[i] != 8:
+                    infos[i].update({k: float(self.terms[i, j]) for j, k in enumerate(N.TERM_NAMES[:5])})
+        if dones.any():
+            ids = np.nonzero(dones)[0]
+            ep_ret, ep_len, reasons = self.ep_return[ids].copy(), self.ep_len[ids].copy(), self.reason[ids].copy()
+            self.terminal_obs[ids] = self.obs[ids]
+            self._counter += 1
+            self.hp.reset_host(n, self.idx, self.ep_len, self.clip, self.obs, mask=self.done, qpos=self.qpos,
+                               qvel=self.qvel, ep_return=self.ep_return, seed=self._seed, counter=self._counter)
+            for k, i in enumerate(ids):
+                infos[i]["terminal_observation"] = self.terminal_obs[i].copy()
+                infos[i]["TimeLimit.truncated"] = bool(reasons[k] == 5)
+                if reasons[k] not in (0, 8):
+                    infos[i]["done_reason"] = N.DONE_REASONS[reasons[k]]
+                infos[i]["episode"] = {"r": float(ep_ret[k]), "l": int(ep_len[k])}
+        return self.obs.copy(), rews, dones, infos
+
+    def step(self, actions, force_state=None):
+        self.step_async(actions, force_state)
+        return self.step_wait()
+
+    def close(self):
+        self.hp.close()
+
+    def get_attr(self, name, indices=None):
+        idx = range(self.num_envs) if indices is None else ([indices] if isinstance(indices, int) else indices)
+        return [getattr(self, name) for _ in idx]
+
+    def set_attr(self, name, value, indices=None):
+        setattr(self, name, value)
+
+    def env_method(self, method_name, *args, indices=None, **kwargs):
+        idx = range(self.num_envs) if indices is None else ([indices] if isinstance(indices, int) else indices)
+        return [getattr(self, method_name)(*args, **kwargs) for _ in idx]
+
+    def env_is_wrapped(self, wrapper_class, indices=None):
+        idx = range(self.num_envs) if indices is None else ([indices] if isinstance(indices, int) else indices)
+        return [False for _ in idx]
+
+    def render(self, mode=None):
+        return None  # graphics stack unavailable on this box; the reference renders through mujoco_py (deepmimic_env.py:527-538)
+
+    # ------------------------------------------------------------------ device-resident path
+    def device_buffers(self):
+        """Allocate (once) torch CUDA tensors mirroring the per-env state for step_tensors()."""
+        if self._dev is None:
+            import torch
+            dev = torch.device("cuda", self.device)
+            d, n = self.hp.dims, self.num_envs
+            t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+            self._dev = dict(idx=t(self.idx), ep_len=t(self.ep_len), clip=t(self.clip), ep_return=t(self.ep_return),
+                             obs=torch.zeros(n, d.obs_dim, device=dev), reward=torch.zeros(n, device=dev),
+                             done=torch.zeros(n, dtype=torch.uint8, device=dev),
+                             reason=torch.zeros(n, dtype=torch.uint8, device=dev),
+                             torque=torch.zeros(n, d.nu, device=dev), terminal_obs=torch.zeros(n, d.obs_dim, device=dev),
+                             qpos=t(self.qpos), qvel=t(self.qvel))
+        return self._dev
+
+    def step_tensors(self, actions, qpos, qvel, contact=None, auto_reset=True, stats=False):
+        """Resident path: everything stays on the GPU; returns (obs, reward, done) tensors owned by the env.
+        With auto_reset, done envs are re-initialised by a masked reset launch (their previous observation goes to
+        device_buffers()['terminal_obs'], their reference state to ['qpos'] / ['qvel'])."""
+        b = self.device_buffers()
+        n = self.num_envs
+        self.hp.step(n, qpos, qvel, actions, contact, b["idx"], b["ep_len"], b["clip"], b["obs"], b["reward"], b["done"],
+                     b["reason"], b["torque"], None, b["ep_return"], stats=stats)
+        if auto_reset:
+            self._counter += 1
+            self.hp.reset(n, b["idx"], b["ep_len"], b["clip"], b["obs"], mask=b["done"], qpos=b["qpos"], qvel=b["qvel"],
+                          ep_return=b["ep_return"], seed=self._seed, counter=self._counter, terminal_obs=b["terminal_obs"])
+        return b["obs"], b["reward"], b["done"]
