@@ -65,10 +65,10 @@ class ClockSampler(threading.Thread):
 
     def __init__(self, gpu):
         super().__init__(daemon=True)
-        self.gpu, self.rows, self._stop = gpu, [], threading.Event()
+        self.gpu, self.rows, self._halt = gpu, [], threading.Event()
 
     def run(self):
-        while not self._stop.is_set():
+        while not self._halt.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
                                      capture_output=True, text=True, timeout=5).stdout.strip()
@@ -76,10 +76,10 @@ class ClockSampler(threading.Thread):
                     self.rows.append([x.strip() for x in out.split(",")])
             except Exception:
                 pass
-            self._stop.wait(0.05)
+            self._halt.wait(0.05)
 
     def stop(self):
-        self._stop.set()
+        self._halt.set()
         self.join(timeout=6)
         sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
         mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
@@ -176,6 +176,7 @@ class Workload:
         self.ep_return = torch.zeros(self.B, n_envs, device=device)
         self.stats = not args.no_stats
         self.i = 0
+        self._prepared = None
 
     def restore(self):
         self.s["idx"].copy_(self.idx0)
@@ -184,8 +185,13 @@ class Workload:
     def step(self):
         b = self.i % self.B
         self.i += 1
+        if self._prepared is None:
+            self._prepared = [self._prepare(k) for k in range(self.B)]
+        self.hp.step_prepared(self._prepared[b])
+
+    def _prepare(self, b):
         s = self.s
-        self.hp.step(self.n, s["qpos"][b], s["qvel"][b], s["action"][b], s["contact"][b], s["idx"][b], s["ep_len"][b],
+        return self.hp.prepare_step(self.n, s["qpos"][b], s["qvel"][b], s["action"][b], s["contact"][b], s["idx"][b], s["ep_len"][b],
                      s["clip"][b], self.obs[b], self.reward[b], self.done[b], self.reason[b], self.torque[b], None,
                      self.ep_return[b], soa_ld=(self.n if self.soa else 0), stats=self.stats)
 

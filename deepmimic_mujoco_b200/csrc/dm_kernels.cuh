@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(128) step_strided_kernel(const __grid_constant
     st.clip = p.clip ? p.clip[env] : 0;
     const uint32_t contact = p.contact ? p.contact[env] : 0u;
     StepOut so;
-    env_step<KIND, Rb, StridedIO, TERMS>(io, p.cs, st, contact, so);
+    env_step<KIND, Rb, StridedIO, TERMS>(io, p.cs, p.cs.rows, st, contact, so);
     finish_env<KIND, Rb, TERMS>(p, env, st, so);
   }
 }

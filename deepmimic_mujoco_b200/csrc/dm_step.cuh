@@ -12,18 +12,25 @@ namespace dm {
 // ---- clip tables -------------------------------------------------------------------------
 // One packed fp32 row per mocap frame holding only what a step reads (all target-side
 // quantities are precomputed once per frame by the table builder):
-//   [0, NSEL)            q*   selected joint angles          (deepmimic_env.py:200,208)
-//   [NSEL, 2 NSEL)       v*   selected joint velocities      (:202,210)
-//   2 NSEL + 0, + 1      roll*, pitch* of the root quaternion (:218-219)
-//   2 NSEL + 2 .. + 13   4 end-effector geom_xpos*           (:232)
-//   2 NSEL + 14 .. + 16  COM* = sum(m * body_xpos*) / sum(m) (:235-237)
-//   2 NSEL + 17, + 18    root linear velocity v*_xy          (combined_env.py:344)
-// padded to a multiple of 4 floats so rows are 16-byte aligned.
+//   [0, NSEL)            q*   selected joint angles          (deepmimic_env.py:200,208)   (block padded to NSELP)
+//   [NSELP, NSELP+NSEL)  v*   selected joint velocities      (:202,210)                   (block padded to NSELP)
+//   2 NSELP + 0, + 1     roll*, pitch* of the root quaternion (:218-219)
+//   2 NSELP + 2 .. + 13  4 end-effector geom_xpos*           (:232)
+//   2 NSELP + 14 .. + 16 COM* = sum(m * body_xpos*) / sum(m) (:235-237)
+//   2 NSELP + 17, + 18   root linear velocity v*_xy          (combined_env.py:344)
+// Rows are 16-byte aligned and a multiple of 16 bytes long.
 template <class Rb>
 struct RowLayout {
-  static constexpr int Q = 0, V = Rb::NSEL, ROLL = 2 * Rb::NSEL, PITCH = ROLL + 1, EE = ROLL + 2, COM = ROLL + 14,
-                       VXY = ROLL + 17, USED = ROLL + 19, STRIDE = (USED + 3) / 4 * 4;
+  // the two joint blocks are padded to a multiple of 4 floats so that every read of a row is a 128-bit load
+  static constexpr int NSELP = (Rb::NSEL + 3) / 4 * 4;
+  static constexpr int Q = 0, V = NSELP, ROLL = 2 * NSELP, PITCH = ROLL + 1, EE = ROLL + 2, COM = ROLL + 14,
+                       VXY = ROLL + 17, USED = ROLL + 19, STRIDE = ROLL + 20;
 };
+
+struct alignas(16) Vec4 {
+  float v[4];
+};
+DM_HD Vec4 ld4(const float* p) { return *reinterpret_cast<const Vec4*>(p); }
 
 enum : int { CLIP_FLOOR = 1, CLIP_ACYCLIC = 2, CLIP_G1_RUN = 4 };
 enum : int { KIND_SINGLE = 0, KIND_COMBINED = 1 };
@@ -102,12 +109,7 @@ DM_HD void write_obs(IO& io, const FkOut<float>& fk, const float* root_rpy, uint
     dm_rpy(fk.tq[0], fk.tq[1], fk.tq[2], fk.tq[3], roll, pitch, yaw);
   }
   float sy, cy;
-#if defined(__CUDA_ARCH__)
-  sincosf(-yaw, &sy, &cy);
-#else
-  sy = sinf(-yaw);
-  cy = cosf(-yaw);
-#endif
+  dm_sincos_f(-yaw, sy, cy);
   const float vx = cy * fk.cvel[3] - sy * fk.cvel[4];
   const float vy = sy * fk.cvel[3] + cy * fk.cvel[4];
   put(L::TORSO + 0, roll * 0.1f);
@@ -161,6 +163,7 @@ DM_HD void write_torque(IO& io) {
 // ---- imitation reward (calc_imitation_reward) ---------------------------------------------
 struct RewardMid {
   float sum_dq, max_dq, d_roll, d_pitch;
+  float vx_ref, vy_ref;  // v*_xy of the frame (task reward of the combined env)
 };
 
 template <class Rb, class IO, bool WANT_COM>
@@ -170,32 +173,44 @@ DM_HD float imitation_reward(const IO& io, const FkOut<float>& fk, const float* 
   float e_q = 0.0f, e_v = 0.0f, mx = 0.0f;
   int nlim = 0;
 #pragma unroll
-  for (int k = 0; k < Rb::NSEL; ++k) {
-    const float q = io.qpos(Rb::sel_q(k));
-    const float d = fabsf(q - row[RL::Q + k]);
-    e_q += d;
-    mx = dm_max_nan(mx, d);
-    e_v += fabsf(row[RL::V + k] - io.qvel(Rb::sel_q(k) - 1));
-    nlim += (q <= Rb::lim_lo(k)) + (q >= Rb::lim_hi(k));
+  for (int c = 0; c < RL::NSELP / 4; ++c) {
+    const Vec4 tq = ld4(row + RL::Q + 4 * c), tv = ld4(row + RL::V + 4 * c);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int k = 4 * c + u;
+      if (k < Rb::NSEL) {
+        const float q = io.qpos(Rb::sel_q(k));
+        const float d = fabsf(q - tq.v[u]);
+        e_q += d;
+        mx = dm_max_nan(mx, d);
+        e_v += fabsf(tv.v[u] - io.qvel(Rb::sel_q(k) - 1));
+        nlim += (q <= Rb::lim_lo(k)) + (q >= Rb::lim_hi(k));
+      }
+    }
   }
+  Vec4 tail[5];  // roll*, pitch*, ee*[12], com*[3], vxy*[2], pad
+#pragma unroll
+  for (int c = 0; c < 5; ++c) tail[c] = ld4(row + RL::ROLL + 4 * c);
+  auto T = [&](int i) { return tail[i >> 2].v[i & 3]; };
   const float roll = root_rpy[0], pitch = root_rpy[1];
+  mid.vx_ref = T(17);
+  mid.vy_ref = T(18);
   mid.sum_dq = e_q;
   mid.max_dq = mx;
-  mid.d_roll = fabsf(roll - row[RL::ROLL]);
-  mid.d_pitch = fabsf(pitch - row[RL::PITCH]);
+  mid.d_roll = fabsf(roll - T(0));
+  mid.d_pitch = fabsf(pitch - T(1));
   const float r_pose = expf(-(e_q + mid.d_pitch));
   const float r_vel = expf(-0.1f * e_v);
   float e_ee = 0.0f;
 #pragma unroll
   for (int k = 0; k < 12; ++k) {
-    const float d = fk.ee[k] - row[RL::EE + k];
+    const float d = fk.ee[k] - T(2 + k);
     e_ee = fmaf(d, d, e_ee);
   }
   const float r_ee = expf(-40.0f * e_ee);
   float r_com = 0.0f;
   if (WANT_COM) {
-    const float dx = row[RL::COM + 0] - fk.com_xpos[0], dy = row[RL::COM + 1] - fk.com_xpos[1],
-                dz = row[RL::COM + 2] - fk.com_xpos[2];
+    const float dx = T(14) - fk.com_xpos[0], dy = T(15) - fk.com_xpos[1], dz = T(16) - fk.com_xpos[2];
     r_com = expf(-10.0f * (dx * dx + dy * dy + dz * dz));
   }
   const float qlim = float(nlim) / float(Rb::NSEL);
@@ -210,14 +225,14 @@ DM_HD float imitation_reward(const IO& io, const FkOut<float>& fk, const float* 
 
 // ---- one environment step --------------------------------------------------------------------
 template <int KIND, class Rb, class IO, bool WANT_TERMS>
-DM_HD void env_step(IO& io, const ClipSet& cs, EnvState& st, uint32_t contact, StepOut& so) {
+DM_HD void env_step(IO& io, const ClipSet& cs, const float* __restrict__ rows, EnvState& st, uint32_t contact, StepOut& so) {
   using RL = RowLayout<Rb>;
   using OL = ObsLayout<KIND, Rb>;
   const int clip0 = st.clip;
   const ClipDesc cd = cs.clip[clip0];
   const int frame = (KIND == KIND_SINGLE) ? st.idx : (st.idx % cd.len);
   const int row_i = cd.row0 + (cd.fixed_row >= 0 ? cd.fixed_row : frame);
-  const float* __restrict__ row = cs.rows + size_t(row_i) * RL::STRIDE;
+  const float* __restrict__ row = rows + size_t(row_i) * RL::STRIDE;
 
   write_torque<Rb>(io);
 
@@ -258,7 +273,7 @@ DM_HD void env_step(IO& io, const ClipSet& cs, EnvState& st, uint32_t contact, S
   } else {
     float task = 0.0f, im = imit;
     if (clip0 == C_WALK || clip0 == C_RUN) {  // combined_env.py:340-347
-      const float dx = row[RL::VXY + 0] - io.qvel(0), dy = row[RL::VXY + 1] - io.qvel(1);
+      const float dx = mid.vx_ref - io.qvel(0), dy = mid.vy_ref - io.qvel(1);
       task = expf(-10.0f * sqrtf(dx * dx + dy * dy));
     }
     if (clip0 == C_TO_GETUP) {  // :348-352

@@ -17,7 +17,7 @@ using namespace dm;
 static thread_local std::string g_last_error;
 
 struct dm_handle {
-  int device = 0, robot = 0, kind = 0;
+  int device = 0, robot = 0, kind = 0, num_sms = 148;
   dm_dims_t dims{};
   std::string err;
   // clip tables
@@ -85,6 +85,7 @@ extern "C" int dm_create(int device, int robot, int env_kind, dm_handle** out) {
   if (device < 0 || device >= ndev) return fail(nullptr, DM_E_ARG, "dm_create: device %d out of range (%d devices)", device, ndev);
   CU(nullptr, cudaSetDevice(device));
   dm_handle* h = new dm_handle();
+  cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device);
   h->device = device;
   h->robot = robot;
   h->kind = env_kind;
@@ -244,11 +245,16 @@ static void timing_end(dm_handle* h, cudaStream_t s) {
   h->ev_used++;
 }
 
+template <class T>
+static T* off(T* p, long long n) { return p ? p + n : p; }
+
 static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
   if (a->n == 0) return DM_OK;
   return dispatch(h, [&](auto rb, auto kind) -> int {
     using Rb = decltype(rb);
     constexpr int KIND = decltype(kind)::value;
+    using OL = ObsLayout<KIND, Rb>;
+    using TC = TileCfg<KIND, Rb>;
     StepParams p{};
     p.n = a->n;
     p.aos = a->layout == DM_LAYOUT_AOS;
@@ -258,21 +264,67 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
     p.obs = a->obs; p.reward = a->reward; p.done = a->done; p.reason = a->reason;
     p.torque = a->torque; p.terms = a->terms; p.ep_return = a->ep_return;
     p.cs = h->cs;
-    const int block = 128;
-    const int grid = (a->n + block - 1) / block;
+    // K1b (shared-memory tiles + TMA bulk loads) for the full tiles of a row-major batch, K1a for the rest
+    const bool aligned = ((reinterpret_cast<uintptr_t>(a->qpos) | reinterpret_cast<uintptr_t>(a->qvel)) & 15u) == 0;
+    int tiled = 0;
+    if (p.aos && h->variant != 0 && aligned && a->n >= TC::TE) tiled = a->n / TC::TE * TC::TE;
     timing_begin(h, s);
-    if (a->terms) step_strided_kernel<KIND, Rb, true><<<grid, block, 0, s>>>(p);
-    else step_strided_kernel<KIND, Rb, false><<<grid, block, 0, s>>>(p);
-    timing_end(h, s);
-    h->launches++;
-    CU(h, cudaGetLastError());
-    if (a->accumulate_stats) {
-      StatsParams sp{a->n, h->dims.obs_dim, p.es, p.aos, a->obs, a->reward, a->done, a->ep_return, a->ep_len, h->d_stats};
-      const int sgrid = (a->n + 2047) / 2048 < 1 ? 1 : (a->n + 2047) / 2048;
-      stats_kernel<<<sgrid > 1184 ? 1184 : sgrid, dim3(32, 8), 0, s>>>(sp);
+    if (tiled) {
+      StepParams q = p;
+      q.n = tiled;
+      const int n_tiles = tiled / TC::TE;
+      const size_t table_bytes = sizeof(float) * (size_t)h->total_rows * RowLayout<Rb>::STRIDE;
+      const bool table_smem = TC::FIXED_BYTES + table_bytes + 2 * TC::GROUP_BYTES <= TC::SMEM_BUDGET;
+      int G = (int)((TC::SMEM_BUDGET - TC::FIXED_BYTES - (table_smem ? table_bytes : 0)) / TC::GROUP_BYTES);
+      G = G > TC::MAXG ? TC::MAXG : G;
+      const int want = (n_tiles + h->num_sms - 1) / h->num_sms;  // spread small batches over all SMs first
+      G = want < G ? (want < 1 ? 1 : want) : G;
+      const int grid = (n_tiles + G - 1) / G < h->num_sms ? (n_tiles + G - 1) / G : h->num_sms;
+      const size_t smem = TC::FIXED_BYTES + (table_smem ? table_bytes : 0) + (size_t)G * TC::GROUP_BYTES;
+      TileExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float))};
+      auto launch = [&](auto kern) -> cudaError_t {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        kern<<<grid, G * TC::TE, smem, s>>>(q, ex);
+        return cudaGetLastError();
+      };
+      auto pick = [&](auto terms, auto stats) -> cudaError_t {
+        constexpr bool T = decltype(terms)::value, S = decltype(stats)::value;
+        return table_smem ? launch(step_tile_kernel<KIND, Rb, T, S, true>) : launch(step_tile_kernel<KIND, Rb, T, S, false>);
+      };
+      using std::true_type; using std::false_type;
+      cudaError_t e = a->terms ? (a->accumulate_stats ? pick(true_type{}, true_type{}) : pick(true_type{}, false_type{}))
+                               : (a->accumulate_stats ? pick(false_type{}, true_type{}) : pick(false_type{}, false_type{}));
+      CU(h, e);
+      h->launches++;
+    }
+    const int rest = a->n - tiled;
+    if (rest) {
+      StepParams q = p;
+      q.n = rest;
+      if (tiled) {  // only reachable for AoS
+        q.qpos = off(p.qpos, (long long)tiled * Rb::NQ); q.qvel = off(p.qvel, (long long)tiled * Rb::NV);
+        q.action = off(p.action, (long long)tiled * Rb::NA); q.contact = off(p.contact, tiled);
+        q.idx = off(p.idx, tiled); q.ep_len = off(p.ep_len, tiled); q.clip = off(p.clip, tiled);
+        q.obs = off(p.obs, (long long)tiled * OL::DIM); q.reward = off(p.reward, tiled); q.done = off(p.done, tiled);
+        q.reason = off(p.reason, tiled); q.torque = off(p.torque, (long long)tiled * Rb::NU);
+        q.terms = off(p.terms, (long long)tiled * 8); q.ep_return = off(p.ep_return, tiled);
+      }
+      const int block = 128, grid = (rest + block - 1) / block;
+      if (a->terms) step_strided_kernel<KIND, Rb, true><<<grid, block, 0, s>>>(q);
+      else step_strided_kernel<KIND, Rb, false><<<grid, block, 0, s>>>(q);
       h->launches++;
       CU(h, cudaGetLastError());
+      if (a->accumulate_stats) {
+        StatsParams sp{rest, h->dims.obs_dim, q.es, q.aos, q.obs, q.reward, q.done, q.ep_return, q.ep_len, h->d_stats};
+        int sgrid = (rest + 2047) / 2048;
+        sgrid = sgrid < 1 ? 1 : (sgrid > 1184 ? 1184 : sgrid);
+        stats_kernel<<<sgrid, dim3(32, 8), 0, s>>>(sp);
+        h->launches++;
+        CU(h, cudaGetLastError());
+      }
     }
+    timing_end(h, s);
     return DM_OK;
   });
 }

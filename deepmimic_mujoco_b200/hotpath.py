@@ -154,6 +154,21 @@ class HotPath:
                             ep_return, soa_ld, stats, stream)
         N.check(self.L.dm_step(self.h, C.byref(a)), self.h, "dm_step")
 
+    def prepare_step(self, n, qpos, qvel, action, contact, idx, ep_len, clip, obs, reward, done, reason=None, torque=None,
+                     terms=None, ep_return=None, soa_ld=0, stats=False, stream=None):
+        """Build the argument block once for buffers that are reused every step (keeps the per-step host cost to a
+        single foreign call; see step_prepared)."""
+        if stream is None:
+            import torch
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        return self._step_args(n, qpos, qvel, action, contact, idx, ep_len, clip, obs, reward, done, reason, torque, terms,
+                               ep_return, soa_ld, stats, stream)
+
+    def step_prepared(self, args):
+        rc = self.L.dm_step(self.h, C.byref(args))
+        if rc:
+            N.check(rc, self.h, "dm_step")
+
     def step_host(self, n, qpos, qvel, action, contact, idx, ep_len, clip, obs, reward, done, reason=None, torque=None,
                   terms=None, ep_return=None, stats=False):
         """Host buffers (C-contiguous numpy).  Returns (h2d_bytes, d2h_bytes)."""

@@ -46,7 +46,7 @@ static int run(int n_clips, const dm_clip_t* clips, int n, const float* qpos, co
                torque ? torque + (size_t)e * Rb::NU : nullptr};
     EnvState st{idx[e], ep_len[e], clip ? clip[e] : 0};
     StepOut so;
-    env_step<KIND, Rb, ArrayIO, true>(io, cs, st, contact ? contact[e] : 0u, so);
+    env_step<KIND, Rb, ArrayIO, true>(io, cs, cs.rows, st, contact ? contact[e] : 0u, so);
     idx[e] = st.idx; ep_len[e] = st.ep_len;
     if (clip && KIND == KIND_COMBINED) clip[e] = st.clip;
     reward[e] = so.reward; done[e] = so.done; reason[e] = so.reason;
