@@ -237,17 +237,21 @@ def timed_region(wl, steps, warmup, world, allreduce_every, stats_t):
 
 
 def kernel_time(wl, steps):
-    """Average device time of the step kernel alone (CUDA events recorded by the library on the launch stream)."""
+    """Average device time of one step's kernel work: `steps` launches queued back to back on torch's current stream,
+    bracketed by CUDA events on that stream (the library launches on the stream it is handed).  Per-launch event
+    pairs would fold host launch latency into short kernels, so the bracket spans the whole queue."""
     import torch
     wl.restore()
-    wl.hp.set_timing(True)
-    wl.hp.kernel_time(reset=True)
-    for _ in range(steps):
+    for _ in range(3):
         wl.step()
     torch.cuda.synchronize()
-    ms, n = wl.hp.kernel_time(reset=True)
-    wl.hp.set_timing(False)
-    return ms, n
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        wl.step()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps, steps
 
 
 def e2e_region(args, steps, warmup, seed):

@@ -53,7 +53,7 @@ struct StridedIO {
   }
 };
 
-template <int KIND, class Rb, bool TERMS>
+template <int KIND, class Rb, bool TERMS, bool EP_RETURN = true>
 __device__ __forceinline__ void finish_env(const StepParams& p, int env, const EnvState& st, const StepOut& so) {
   p.idx[env] = st.idx;
   p.ep_len[env] = st.ep_len;
@@ -61,7 +61,7 @@ __device__ __forceinline__ void finish_env(const StepParams& p, int env, const E
   p.reward[env] = so.reward;
   p.done[env] = so.done;
   if (p.reason) p.reason[env] = so.reason;
-  if (p.ep_return) p.ep_return[env] += so.raw_reward;
+  if (EP_RETURN && p.ep_return) p.ep_return[env] += so.raw_reward;
   if (TERMS) {
     const long long base = p.aos ? (long long)env * 8 : env;
 #pragma unroll

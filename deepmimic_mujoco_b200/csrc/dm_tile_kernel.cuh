@@ -47,6 +47,9 @@ __device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t
                "l"(src), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
 }
+__device__ __forceinline__ void l2_prefetch(const void* src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void group_sync(int group) {  // named barrier 1 + group, 128 threads
   asm volatile("bar.sync %0, 128;" ::"r"(group + 1) : "memory");
 }
@@ -60,7 +63,9 @@ struct TileCfg {
   static constexpr int QP = TE * Rb::NQ, QV = TE * Rb::NV, CO = TE * NCOMP;
   static constexpr int GROUP_FLOATS = QP + QV + CO + TE / 4;  // + guard flags (1 byte per env)
   static constexpr size_t GROUP_BYTES = sizeof(float) * GROUP_FLOATS;
-  static constexpr size_t FIXED_BYTES = 128;  // mbarriers
+  static constexpr int NUP = (Rb::NU + 3) / 4 * 4;
+  static constexpr size_t FIXED_BYTES = 128 + sizeof(float) * 3 * NUP;  // mbarriers + motor table (gear | lo | hi)
+  static_assert(FIXED_BYTES % 16 == 0, "alignment");
   static constexpr size_t SMEM_BUDGET = 227 * 1024;
 };
 
@@ -93,6 +98,7 @@ __global__ void __launch_bounds__(512, 1) step_tile_kernel(const __grid_constant
   constexpr int NCOLIT = (DIM + 31) / 32;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);  // [0..MAXG) group barriers, [MAXG] table barrier
+  float* s_motor = reinterpret_cast<float*>(smem_raw + 128);  // [3][NUP]
   float* s_table = reinterpret_cast<float*>(smem_raw + TC::FIXED_BYTES);
   const int n_groups = blockDim.x / TE;
   const int tid = threadIdx.x, group = tid / TE, gt = tid % TE, lane = tid & 31, warp = gt >> 5;
@@ -113,16 +119,17 @@ __global__ void __launch_bounds__(512, 1) step_tile_kernel(const __grid_constant
   }
   const float* rows = TABLE_SMEM ? s_table : p.cs.rows;
 
-  // per-lane motor constants of the actuators this lane serves in the torque pass
-  constexpr int NUIT = (Rb::NU + 31) / 32;
-  float m_gear[NUIT], m_lo[NUIT], m_hi[NUIT];
+  // motor constants (gear, ctrlrange) of every actuator, looked up by the flat torque pass
+  for (int k = tid; k < TC::NUP; k += blockDim.x) {
+    float g = 0.0f, lo = 0.0f, hi = 0.0f;
 #pragma unroll
-  for (int it = 0; it < NUIT; ++it) {
-    m_gear[it] = m_lo[it] = m_hi[it] = 0.0f;
-#pragma unroll
-    for (int kk = it * 32; kk < it * 32 + 32 && kk < Rb::NU; ++kk)
-      if (kk == it * 32 + lane) { m_gear[it] = Rb::gear(kk); m_lo[it] = Rb::ctrl_lo(kk); m_hi[it] = Rb::ctrl_hi(kk); }
+    for (int kk = 0; kk < Rb::NU; ++kk)
+      if (kk == k) { g = Rb::gear(kk); lo = Rb::ctrl_lo(kk); hi = Rb::ctrl_hi(kk); }
+    s_motor[k] = g;
+    s_motor[TC::NUP + k] = lo;
+    s_motor[2 * TC::NUP + k] = hi;
   }
+  __syncthreads();
   // statistics carried across tiles
   double a_cs[NCOLIT], a_css[NCOLIT], a_sc[6];
 #pragma unroll
@@ -138,34 +145,77 @@ __global__ void __launch_bounds__(512, 1) step_tile_kernel(const __grid_constant
       mbar_expect_tx(bar, sizeof(float) * (TC::QP + TC::QV));
       tma_load_1d(s_qp, p.qpos + e0 * Rb::NQ, sizeof(float) * TC::QP, bar);
       tma_load_1d(s_qv, p.qvel + e0 * Rb::NV, sizeof(float) * TC::QV, bar);
-    }
-    // ---- action -> torque while the tile is in flight: warps walk rows, lanes walk actuators ----------
-    if (p.torque) {
-#pragma unroll
-      for (int it = 0; it < NUIT; ++it) {
-        const int k = it * 32 + lane;
-        if (k < Rb::NU) {
-#pragma unroll 4
-          for (int r = warp; r < TE; r += 4) {
-            float t = 0.0f;
-            if (k < Rb::NA) {
-              float c = __ldg(p.action + (e0 + r) * Rb::NA + k) * Rb::kActScale;
-              c = c > m_hi[it] ? m_hi[it] : c;
-              c = c < m_lo[it] ? m_lo[it] : c;
-              t = m_gear[it] * c;
-            }
-            p.torque[(e0 + r) * Rb::NU + k] = t;
-          }
-        }
+      const int nxt = tile + gridDim.x * n_groups;  // pull the group's next tile into L2 behind this one
+      if (nxt < x.n_tiles) {
+        const long long n0 = (long long)nxt * TE;
+        l2_prefetch(p.qpos + n0 * Rb::NQ, sizeof(float) * TC::QP);
+        l2_prefetch(p.qvel + n0 * Rb::NV, sizeof(float) * TC::QV);
+        l2_prefetch(p.action + n0 * Rb::NA, sizeof(float) * TE * Rb::NA);
       }
     }
-    // ---- per-environment step out of shared memory --------------------------------------------------
+    // ---- per-env scalars: issue the loads now, they are consumed after the TMA wait -------------------------
     const int env = int(e0) + gt;
     EnvState st;
     st.idx = p.idx[env];
     st.ep_len = p.ep_len[env];
     st.clip = p.clip ? p.clip[env] : 0;
     const uint32_t contact = p.contact ? p.contact[env] : 0u;
+    const float ep_ret0 = p.ep_return ? p.ep_return[env] : 0.0f;
+    // ---- action -> torque while the tile is in flight: a flat, fully coalesced pass over the [TE, NA] tile with
+    //      every load issued before the first use (the tile is contiguous in the row-major action array) --------
+    if (p.torque) {
+      if (Rb::NA == Rb::NU && Rb::NA % 4 == 0) {  // 128-bit path: chunk c covers actuators 4 (c mod NA/4) .. + 3
+        constexpr int CH = TE * Rb::NA / 4, PER = (CH + TE - 1) / TE, K4 = Rb::NA / 4;
+        const float4* a4 = reinterpret_cast<const float4*>(p.action + e0 * Rb::NA);
+        float4* t4 = reinterpret_cast<float4*>(p.torque + e0 * Rb::NU);
+        float4 v[PER];
+#pragma unroll
+        for (int m = 0; m < PER; ++m)
+          if (gt + m * TE < CH) v[m] = __ldg(a4 + gt + m * TE);
+#pragma unroll
+        for (int m = 0; m < PER; ++m) {
+          const int c = gt + m * TE;
+          if (c < CH) {
+            const int k0 = (c % K4) * 4;
+            const float4 g = *reinterpret_cast<const float4*>(s_motor + k0);
+            const float4 lo = *reinterpret_cast<const float4*>(s_motor + TC::NUP + k0);
+            const float4 hi = *reinterpret_cast<const float4*>(s_motor + 2 * TC::NUP + k0);
+            float4 o;
+            float c0 = v[m].x * Rb::kActScale, c1 = v[m].y * Rb::kActScale, c2 = v[m].z * Rb::kActScale, c3 = v[m].w * Rb::kActScale;
+            c0 = c0 > hi.x ? hi.x : c0; c0 = c0 < lo.x ? lo.x : c0; o.x = g.x * c0;
+            c1 = c1 > hi.y ? hi.y : c1; c1 = c1 < lo.y ? lo.y : c1; o.y = g.y * c1;
+            c2 = c2 > hi.z ? hi.z : c2; c2 = c2 < lo.z ? lo.z : c2; o.z = g.z * c2;
+            c3 = c3 > hi.w ? hi.w : c3; c3 = c3 < lo.w ? lo.w : c3; o.w = g.w * c3;
+            t4[c] = o;
+          }
+        }
+      } else {  // scalar flat path: output element o = (row, actuator); hand actuators get zero torque
+        constexpr int TOT = TE * Rb::NU, PER = (TOT + TE - 1) / TE, HALF = (PER + 1) / 2;
+        const float* arow = p.action + e0 * Rb::NA;
+        float* trow = p.torque + e0 * Rb::NU;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          float v[HALF];
+#pragma unroll
+          for (int m = 0; m < HALF; ++m) {
+            const int o = gt + (h * HALF + m) * TE, r = o / Rb::NU, k = o - r * Rb::NU;
+            v[m] = (h * HALF + m < PER && o < TOT && k < Rb::NA) ? __ldg(arow + r * Rb::NA + k) : 0.0f;
+          }
+#pragma unroll
+          for (int m = 0; m < HALF; ++m) {
+            const int o = gt + (h * HALF + m) * TE, r = o / Rb::NU, k = o - r * Rb::NU;
+            if (h * HALF + m < PER && o < TOT) {
+              float c = v[m] * Rb::kActScale;
+              const float hi = s_motor[2 * TC::NUP + k], lo = s_motor[TC::NUP + k];
+              c = c > hi ? hi : c;
+              c = c < lo ? lo : c;
+              trow[o] = k < Rb::NA ? s_motor[k] * c : 0.0f;
+            }
+          }
+        }
+      }
+    }
+    // ---- per-environment step out of shared memory --------------------------------------------------
     if (!table_ready) {
       mbar_wait(bars + TC::MAXG, 0);
       table_ready = true;
@@ -176,14 +226,16 @@ __global__ void __launch_bounds__(512, 1) step_tile_kernel(const __grid_constant
     StepOut so;
     env_step<KIND, Rb, TileIO<KIND, Rb>, TERMS>(io, p.cs, rows, st, contact, so);
     s_guard[gt] = (so.reason == R_OBS_BOUNDS) ? 1 : 0;
-    finish_env<KIND, Rb, TERMS>(p, env, st, so);
+    finish_env<KIND, Rb, TERMS, false>(p, env, st, so);
+    const float ep_ret1 = ep_ret0 + so.raw_reward;
+    if (p.ep_return) p.ep_return[env] = ep_ret1;
     if (STATS) {
       a_sc[0] += 1.0;
       a_sc[1] += so.reward;
       a_sc[2] += double(so.reward) * so.reward;
       if (so.done) {
         a_sc[3] += 1.0;
-        a_sc[4] += p.ep_return ? p.ep_return[env] : 0.0f;
+        a_sc[4] += ep_ret1;
         a_sc[5] += st.ep_len;
       }
     }
