@@ -276,18 +276,28 @@ __global__ void __launch_bounds__(512, 1) step_tile_kernel(const __grid_constant
   }
 
   if (STATS && x.acc) {
+    // CTA-level reduction in shared memory (the tiles are dead by now), then ONE set of fp64 atomics per CTA
+    __syncthreads();
+    double* sc = reinterpret_cast<double*>(s_table + (TABLE_SMEM ? x.table_floats : 0));  // [n_warps][2 * NCOLIT * 32 + 6]
+    constexpr int W = 2 * NCOLIT * 32 + 6;
+    const int wid = tid >> 5, n_warps = blockDim.x >> 5;
+#pragma unroll
+    for (int it = 0; it < NCOLIT; ++it) {
+      sc[wid * W + it * 32 + lane] = a_cs[it];
+      sc[wid * W + NCOLIT * 32 + it * 32 + lane] = a_css[it];
+    }
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
       const double v = warp_sum(a_sc[k]);
-      if (lane == 0 && v != 0.0) atomicAdd(x.acc + k, v);
+      if (lane == 0) sc[wid * W + 2 * NCOLIT * 32 + k] = v;
     }
-#pragma unroll
-    for (int it = 0; it < NCOLIT; ++it) {
-      const int j = it * 32 + lane;
-      if (j < DIM && a_css[it] != 0.0) {
-        atomicAdd(x.acc + 6 + j, a_cs[it]);
-        atomicAdd(x.acc + 6 + DIM + j, a_css[it]);
-      }
+    __syncthreads();
+    for (int j = tid; j < 2 * DIM + 6; j += blockDim.x) {
+      // j < 6: scalars; then sum obs[DIM]; then sum obs^2[DIM]
+      const int col = j < 6 ? 2 * NCOLIT * 32 + j : (j < 6 + DIM ? j - 6 : NCOLIT * 32 + (j - 6 - DIM));
+      double v = 0.0;
+      for (int w = 0; w < n_warps; ++w) v += sc[w * W + col];
+      if (v != 0.0) atomicAdd(x.acc + j, v);
     }
   }
 }
