@@ -5,6 +5,8 @@
 // :193-256 (calc_imitation_reward), :335-484 (DPEnv.step); src/combined_env.py:246-505
 // (DPCombinedEnv.step / _get_obs); restated for float64 in oracle/envs.py.
 #pragma once
+#include <type_traits>
+
 #include "dm_math.cuh"
 
 namespace dm {
@@ -223,6 +225,13 @@ DM_HD float imitation_reward(const IO& io, const FkOut<float>& fk, const float* 
   return 0.75f * r_pose + 0.1f * r_vel + 0.15f * r_ee + (-0.1f) * qlim;
 }
 
+// accessors that emit the observation themselves (the warp kernel assembles it in shared memory) declare
+// `static constexpr bool kZeroOnGuard = false` and zero the row on R_OBS_BOUNDS when they write it
+template <class IO, class = void>
+struct io_zeroes_on_guard : std::true_type {};
+template <class IO>
+struct io_zeroes_on_guard<IO, std::enable_if_t<!IO::kZeroOnGuard>> : std::false_type {};
+
 // ---- one environment step --------------------------------------------------------------------
 template <int KIND, class Rb, class IO, bool WANT_TERMS>
 DM_HD void env_step(IO& io, const ClipSet& cs, const float* __restrict__ rows, EnvState& st, uint32_t contact, StepOut& so) {
@@ -311,8 +320,10 @@ DM_HD void env_step(IO& io, const ClipSet& cs, const float* __restrict__ rows, E
   // observation bounds guard (deepmimic_env.py:465-476, combined_env.py:474-485): zero observation,
   // zero reward, done, empty info -- evaluated after the counters advanced
   if (omax > 100.0f || omin < -100.0f) {
+    if constexpr (io_zeroes_on_guard<IO>::value) {
 #pragma unroll 1
-    for (int j = 0; j < OL::DIM; ++j) io.obs(j, 0.0f);
+      for (int j = 0; j < OL::DIM; ++j) io.obs(j, 0.0f);
+    }
     so.reward = 0.0f;
     so.done = 1;
     so.reason = R_OBS_BOUNDS;

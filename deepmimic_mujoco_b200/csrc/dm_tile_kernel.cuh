@@ -1,21 +1,35 @@
-// K1b: row-major (AoS) step kernel -- persistent CTAs, shared-memory tiles, TMA bulk loads.
+// K1b: row-major (AoS) step kernel -- persistent CTAs, shared-memory tiles, TMA in, in-place tile, TMA out.
 //
-// Launch shape: one CTA per SM, G groups of 128 threads per CTA (G chosen from the shared-memory budget).
-// Each group walks tiles of TE = 128 consecutive environments (tile = cta * G + group, stride grid * G):
-//   * the tile's qpos / qvel rows are contiguous in the row-major arrays, so each is ONE 1-D TMA bulk copy
-//     (cp.async.bulk global -> shared, completion on the group's mbarrier; SASS: UBLKCP);
-//   * the packed clip table is staged ONCE per CTA in shared memory by the same mechanism (when it fits), so
-//     the per-environment gather of a random mocap frame is a 128-bit shared-memory load, not an L1 gather;
-//   * every thread steps its own environment out of shared memory (row stride nq / nv words);
-//   * nothing is written to global memory with a row stride: the observation is emitted by a cooperative,
-//     fully coalesced pass (warps walk rows, lanes walk columns) that takes the joint blocks straight from
-//     the staged qpos / qvel tiles and the computed entries from a small per-env tile; action -> torque is a
-//     second cooperative pass, global -> global, one lane per actuator, issued while the TMA is in flight;
-//     reward / done / reason / counters are one coalesced store per array.
-// Groups synchronise among themselves only (named barriers), so one group's TMA wait overlaps the others'
-// arithmetic.  Shared memory per environment is ~320 B (humanoid3d), i.e. 4 tiles + the table per SM.
-// The observation-normaliser moments are accumulated by the cooperative pass (per-lane column sums kept in
-// registers across ALL tiles of the group) and flushed with one set of fp64 atomics per CTA.
+// Launch shape: one CTA per SM, G groups of 128 threads per CTA.  Each group walks tiles of TE = 128 consecutive
+// environments (tile = cta * G + group, stride grid * G) and synchronises only with itself (named barriers), so
+// one group's TMA wait overlaps the others' arithmetic.  The four warps of a group sit on the four SM
+// sub-partitions and run in step; groups run out of phase.  Both halves of that matter and were measured
+// (profiles/r01_design_notes.md): the per-environment step is ~2500 straight-line instructions (40-100 KB of
+// SASS, beyond the 32 KB L1.5 instruction cache), so 16 fully autonomous warps each stream the whole kernel from
+// L2 (1.3 "no instruction" stall cycles per issue, 48 % issue utilisation), while a single CTA-wide lock-step
+// tile stalls every warp at once on each global-load latency (42 %).  Four groups of four keep the instruction
+// streams at four and still hide latency.
+// Per tile:
+//   in    the tile's qpos and qvel rows are contiguous in the row-major arrays: two 1-D TMA bulk loads
+//         (cp.async.bulk global -> shared, completion on the group's mbarrier; SASS: UBLKCP); the group's next
+//         tile is pulled into L2 behind them (cp.async.bulk.prefetch.L2);
+//   table the packed clip table is staged ONCE per CTA in shared memory (when it fits), so the per-environment
+//         gather of a mocap frame is a 128-bit shared-memory load;
+//   step  every thread steps its own environment out of shared memory; the computed observation entries stay
+//         in registers;
+//   out   the observation tile [TE, obs_dim] is assembled IN PLACE: every thread first pulls its joint blocks
+//         into registers, the group syncs, every thread writes its finished row over the (now dead) input rows
+//         -- the row stride obs_dim is odd, or 2 mod 32 at worst, so the stores are (nearly) conflict-free --
+//         and one thread issues a single TMA bulk store shared -> global for the whole tile.  Nothing is
+//         written to global memory with a row stride, and an observation entry costs ~2 shared-memory
+//         instructions instead of a trip through a cooperative gather loop;
+//   torque action -> torque is a flat 128-bit pass global -> global issued while the TMA load is in flight;
+//   stats the normaliser moments are column sums of the finished tile read back from shared memory (lanes walk
+//         columns, warps walk rows: conflict-free); five per-environment scalars (1, reward, done, episode
+//         return and length of finished episodes) ride along as extra columns.  The per-thread fp64 running sums
+//         live in shared memory, not registers, and are flushed with one CTA-level reduction and one set of fp64
+//         atomics per CTA.
+// Batches that are not a multiple of 128 environments hand the remainder to the strided kernel (K1a).
 #pragma once
 #include "dm_kernels.cuh"
 
@@ -47,70 +61,104 @@ __device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t
                "l"(src), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
 }
+// 1-D TMA bulk copy shared -> global, tracked by the issuing thread's bulk async-group
+__device__ __forceinline__ void tma_store_1d(void* dst, const void* src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all bulk stores of this thread have finished READING shared memory (the buffer may be overwritten)
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+// generic-proxy writes to shared memory become visible to the async proxy (TMA)
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void l2_prefetch(const void* src, uint32_t bytes) {
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void group_sync(int group) {  // named barrier 1 + group, 128 threads
-  asm volatile("bar.sync %0, 128;" ::"r"(group + 1) : "memory");
 }
 
 template <int KIND, class Rb>
 struct TileCfg {
   using OL = ObsLayout<KIND, Rb>;
+  static constexpr int TE = 128;                       // environments per tile = threads per group
   static constexpr int NCOMP = OL::DIM - 2 * Rb::NJ;  // computed obs entries (torso, contacts, phase, player action)
-  static constexpr int TE = 128;
-  static constexpr int MAXG = 4;
-  static constexpr int QP = TE * Rb::NQ, QV = TE * Rb::NV, CO = TE * NCOMP;
-  static constexpr int GROUP_FLOATS = QP + QV + CO + TE / 4;  // + guard flags (1 byte per env)
-  static constexpr size_t GROUP_BYTES = sizeof(float) * GROUP_FLOATS;
+  static constexpr int ROW = (Rb::NQ + Rb::NV) > OL::DIM ? (Rb::NQ + Rb::NV) : OL::DIM;
+  static constexpr int NXC = 5;                        // extra statistics columns: 1, reward, done, ep_return, ep_len
+  static constexpr int NCOLS = OL::DIM + NXC, NCOLIT = (NCOLS + 31) / 32;
+  // per group: the tile buffer (input rows, later the observation tile), the extra columns, the running sums
+  static constexpr int BUF_FLOATS = TE * ROW, XC_FLOATS = TE * NXC;
+  static constexpr size_t GROUP_BYTES = sizeof(float) * (BUF_FLOATS + XC_FLOATS);
+  static constexpr size_t ACC_BYTES = sizeof(double) * 2 * NCOLIT * TE;  // per group, STATS only
   static constexpr int NUP = (Rb::NU + 3) / 4 * 4;
+  static constexpr int MAXG = 4;
   static constexpr size_t FIXED_BYTES = 128 + sizeof(float) * 3 * NUP;  // mbarriers + motor table (gear | lo | hi)
-  static_assert(FIXED_BYTES % 16 == 0, "alignment");
+  static_assert(FIXED_BYTES % 16 == 0 && GROUP_BYTES % 16 == 0, "alignment");
   static constexpr size_t SMEM_BUDGET = 227 * 1024;
 };
 
-// per-thread accessor into the staged tiles
+// per-thread accessor: inputs from the staged rows, computed observation entries into registers
 template <int KIND, class Rb>
 struct TileIO {
+  static constexpr bool kZeroOnGuard = false;  // the kernel zeroes the row when it writes the tile
+  static constexpr int NCOMP = TileCfg<KIND, Rb>::NCOMP;
   const float* __restrict__ qp;  // this env's qpos row in shared memory
   const float* __restrict__ qv;
-  float* __restrict__ co;        // this env's computed-obs row in shared memory
+  float co[NCOMP];
   __device__ __forceinline__ float qpos(int j) const { return qp[j]; }
   __device__ __forceinline__ float qvel(int j) const { return qv[j]; }
   __device__ __forceinline__ float act(int) const { return 0.0f; }
-  __device__ __forceinline__ void obs(int j, float v) {
-    if (j >= 2 * Rb::NJ) co[j - 2 * Rb::NJ] = v;  // the joint blocks are copied by the cooperative pass
+  __device__ __forceinline__ void obs(int j, float v) {  // j is a compile-time constant after unrolling
+    if (j >= 2 * Rb::NJ) co[j - 2 * Rb::NJ] = v;         // the joint blocks are copied from the staged rows
   }
   __device__ __forceinline__ void tau(int, float) {}
+};
+
+// groups per CTA the kernel is compiled for (register budget = 65536 / (128 G) per thread)
+template <class Rb>
+struct KernelGroups {
+  static constexpr int G = 4;
+};
+template <>
+struct KernelGroups<Robot_unitree_g1> {  // 37 hinges: the joint blocks alone are 74 live registers when the tile is written
+  static constexpr int G = 3;
 };
 
 struct TileExtra {
   double* acc;       // statistics accumulators or NULL
   int n_tiles;       // full tiles in this launch
   int table_floats;  // packed clip table size (floats); staged in shared memory when TABLE_SMEM
+  int l2_prefetch;   // != 0: pull the group's next tile into L2 behind the current one
 };
 
-template <int KIND, class Rb, bool TERMS, bool STATS, bool TABLE_SMEM>
-__global__ void __launch_bounds__(512, 1) step_tile_kernel(const __grid_constant__ StepParams p, const TileExtra x) {
+__device__ __forceinline__ void group_sync(int group) {  // named barrier 1 + group, 128 threads
+  asm volatile("bar.sync %0, 128;" ::"r"(group + 1) : "memory");
+}
+
+template <int KIND, class Rb, bool TERMS, bool STATS, bool TABLE_SMEM, int G>
+__global__ void __launch_bounds__(128 * G, 1) step_tile_kernel(const __grid_constant__ StepParams p, const TileExtra x) {
   using OL = ObsLayout<KIND, Rb>;
   using TC = TileCfg<KIND, Rb>;
-  constexpr int TE = TC::TE, NJ = Rb::NJ, DIM = OL::DIM, NCOMP = TC::NCOMP;
-  constexpr int NCOLIT = (DIM + 31) / 32;
+  constexpr int TE = TC::TE, NJ = Rb::NJ, DIM = OL::DIM, NCOMP = TC::NCOMP, NCOLIT = TC::NCOLIT, NXC = TC::NXC;
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);  // [0..MAXG) group barriers, [MAXG] table barrier
-  float* s_motor = reinterpret_cast<float*>(smem_raw + 128);  // [3][NUP]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);      // [0..MAXG) group barriers, [MAXG] table barrier
+  float* s_motor = reinterpret_cast<float*>(smem_raw + 128);   // [3][NUP]
   float* s_table = reinterpret_cast<float*>(smem_raw + TC::FIXED_BYTES);
   const int n_groups = blockDim.x / TE;
   const int tid = threadIdx.x, group = tid / TE, gt = tid % TE, lane = tid & 31, warp = gt >> 5;
-  float* s_qp = s_table + (TABLE_SMEM ? x.table_floats : 0) + (size_t)group * TC::GROUP_FLOATS;
-  float* s_qv = s_qp + TC::QP;
-  float* s_co = s_qv + TC::QV;
-  unsigned char* s_guard = reinterpret_cast<unsigned char*>(s_co + TC::CO);
+  float* s_groups = s_table + (TABLE_SMEM ? x.table_floats : 0);
+  float* buf = s_groups + (size_t)group * (TC::BUF_FLOATS + TC::XC_FLOATS);
+  float* s_qp = buf;
+  float* s_qv = buf + TE * Rb::NQ;
+  float* s_xc = buf + TC::BUF_FLOATS;  // [TE][NXC]
+  // running column sums of this thread: my_acc[k * TE], k < NCOLIT sums, then NCOLIT sums of squares
+  double* my_acc = reinterpret_cast<double*>(s_groups + (size_t)n_groups * (TC::BUF_FLOATS + TC::XC_FLOATS)) +
+                   (size_t)group * 2 * NCOLIT * TE + gt;
   uint64_t* bar = bars + group;
 
   if (tid == 0) {
     for (int g = 0; g <= TC::MAXG; ++g) mbar_init(bars + g, 1);
     mbar_fence_init();
+  }
+  if (STATS) {
+#pragma unroll
+    for (int k = 0; k < 2 * NCOLIT; ++k) my_acc[k * TE] = 0.0;
   }
   __syncthreads();
   if (TABLE_SMEM && tid == 0) {
@@ -130,48 +178,59 @@ __global__ void __launch_bounds__(512, 1) step_tile_kernel(const __grid_constant
     s_motor[2 * TC::NUP + k] = hi;
   }
   __syncthreads();
-  // statistics carried across tiles
-  double a_cs[NCOLIT], a_css[NCOLIT], a_sc[6];
-#pragma unroll
-  for (int it = 0; it < NCOLIT; ++it) a_cs[it] = a_css[it] = 0.0;
-#pragma unroll
-  for (int k = 0; k < 6; ++k) a_sc[k] = 0.0;
 
   uint32_t parity = 0;
   bool table_ready = !TABLE_SMEM;
-  for (int tile = blockIdx.x * n_groups + group; tile < x.n_tiles; tile += gridDim.x * n_groups) {
+  const int tstride = gridDim.x * n_groups;
+  // Software pipeline through registers: the per-env scalars and (128-bit path) the action chunks of a tile are
+  // loaded one tile AHEAD, right after the previous tile's observation store is issued, so their global-load
+  // latency hides behind the statistics pass and the barrier instead of stalling every warp of the group.
+  constexpr bool kVecTorque = Rb::NA == Rb::NU && Rb::NA % 4 == 0;
+  constexpr int K4 = Rb::NA / 4, CH = TE * Rb::NA / 4, PER = kVecTorque ? (CH + TE - 1) / TE : 1;
+  float4 av[PER];
+  EnvState st_n{0, 0, 0};
+  uint32_t contact_n = 0u;
+  float ep_ret_n = 0.0f;
+  auto load_ahead = [&](int t) {
+    const long long f0 = (long long)t * TE;
+    const int e = int(f0) + gt;
+    st_n.idx = p.idx[e];
+    st_n.ep_len = p.ep_len[e];
+    st_n.clip = p.clip ? p.clip[e] : 0;
+    contact_n = p.contact ? p.contact[e] : 0u;
+    ep_ret_n = p.ep_return ? p.ep_return[e] : 0.0f;
+    if (kVecTorque && p.torque) {
+      const float4* a4 = reinterpret_cast<const float4*>(p.action + f0 * Rb::NA);
+#pragma unroll
+      for (int m = 0; m < PER; ++m)
+        if (gt + m * TE < CH) av[m] = __ldg(a4 + gt + m * TE);
+    }
+  };
+  int tile = blockIdx.x * n_groups + group;
+  if (tile < x.n_tiles) load_ahead(tile);
+  for (; tile < x.n_tiles; tile += tstride) {
     const long long e0 = (long long)tile * TE;
     if (gt == 0) {
-      mbar_expect_tx(bar, sizeof(float) * (TC::QP + TC::QV));
-      tma_load_1d(s_qp, p.qpos + e0 * Rb::NQ, sizeof(float) * TC::QP, bar);
-      tma_load_1d(s_qv, p.qvel + e0 * Rb::NV, sizeof(float) * TC::QV, bar);
-      const int nxt = tile + gridDim.x * n_groups;  // pull the group's next tile into L2 behind this one
-      if (nxt < x.n_tiles) {
+      bulk_wait_read0();  // the previous tile's observation store is done reading this buffer
+      mbar_expect_tx(bar, sizeof(float) * TE * (Rb::NQ + Rb::NV));
+      tma_load_1d(s_qp, p.qpos + e0 * Rb::NQ, sizeof(float) * TE * Rb::NQ, bar);
+      tma_load_1d(s_qv, p.qvel + e0 * Rb::NV, sizeof(float) * TE * Rb::NV, bar);
+      const int nxt = tile + tstride;  // pull the group's next tile into L2 behind this one
+      if (x.l2_prefetch && nxt < x.n_tiles) {
         const long long n0 = (long long)nxt * TE;
-        l2_prefetch(p.qpos + n0 * Rb::NQ, sizeof(float) * TC::QP);
-        l2_prefetch(p.qvel + n0 * Rb::NV, sizeof(float) * TC::QV);
-        l2_prefetch(p.action + n0 * Rb::NA, sizeof(float) * TE * Rb::NA);
+        l2_prefetch(p.qpos + n0 * Rb::NQ, sizeof(float) * TE * Rb::NQ);
+        l2_prefetch(p.qvel + n0 * Rb::NV, sizeof(float) * TE * Rb::NV);
       }
     }
-    // ---- per-env scalars: issue the loads now, they are consumed after the TMA wait -------------------------
     const int env = int(e0) + gt;
-    EnvState st;
-    st.idx = p.idx[env];
-    st.ep_len = p.ep_len[env];
-    st.clip = p.clip ? p.clip[env] : 0;
-    const uint32_t contact = p.contact ? p.contact[env] : 0u;
-    const float ep_ret0 = p.ep_return ? p.ep_return[env] : 0.0f;
-    // ---- action -> torque while the tile is in flight: a flat, fully coalesced pass over the [TE, NA] tile with
-    //      every load issued before the first use (the tile is contiguous in the row-major action array) --------
+    EnvState st = st_n;
+    const uint32_t contact = contact_n;
+    const float ep_ret0 = ep_ret_n;
+    // ---- action -> torque: a flat, fully coalesced pass over the [TE, NA] tile (contiguous in the row-major
+    //      action array) ----------------------------------------------------------------------------------------
     if (p.torque) {
-      if (Rb::NA == Rb::NU && Rb::NA % 4 == 0) {  // 128-bit path: chunk c covers actuators 4 (c mod NA/4) .. + 3
-        constexpr int CH = TE * Rb::NA / 4, PER = (CH + TE - 1) / TE, K4 = Rb::NA / 4;
-        const float4* a4 = reinterpret_cast<const float4*>(p.action + e0 * Rb::NA);
+      if (kVecTorque) {  // 128-bit path: chunk c covers actuators 4 (c mod NA/4) .. + 3; loaded a tile ahead
         float4* t4 = reinterpret_cast<float4*>(p.torque + e0 * Rb::NU);
-        float4 v[PER];
-#pragma unroll
-        for (int m = 0; m < PER; ++m)
-          if (gt + m * TE < CH) v[m] = __ldg(a4 + gt + m * TE);
 #pragma unroll
         for (int m = 0; m < PER; ++m) {
           const int c = gt + m * TE;
@@ -181,7 +240,7 @@ __global__ void __launch_bounds__(512, 1) step_tile_kernel(const __grid_constant
             const float4 lo = *reinterpret_cast<const float4*>(s_motor + TC::NUP + k0);
             const float4 hi = *reinterpret_cast<const float4*>(s_motor + 2 * TC::NUP + k0);
             float4 o;
-            float c0 = v[m].x * Rb::kActScale, c1 = v[m].y * Rb::kActScale, c2 = v[m].z * Rb::kActScale, c3 = v[m].w * Rb::kActScale;
+            float c0 = av[m].x * Rb::kActScale, c1 = av[m].y * Rb::kActScale, c2 = av[m].z * Rb::kActScale, c3 = av[m].w * Rb::kActScale;
             c0 = c0 > hi.x ? hi.x : c0; c0 = c0 < lo.x ? lo.x : c0; o.x = g.x * c0;
             c1 = c1 > hi.y ? hi.y : c1; c1 = c1 < lo.y ? lo.y : c1; o.y = g.y * c1;
             c2 = c2 > hi.z ? hi.z : c2; c2 = c2 < lo.z ? lo.z : c2; o.z = g.z * c2;
@@ -190,7 +249,7 @@ __global__ void __launch_bounds__(512, 1) step_tile_kernel(const __grid_constant
           }
         }
       } else {  // scalar flat path: output element o = (row, actuator); hand actuators get zero torque
-        constexpr int TOT = TE * Rb::NU, PER = (TOT + TE - 1) / TE, HALF = (PER + 1) / 2;
+        constexpr int TOT = TE * Rb::NU, PERS = (TOT + TE - 1) / TE, HALF = (PERS + 1) / 2;
         const float* arow = p.action + e0 * Rb::NA;
         float* trow = p.torque + e0 * Rb::NU;
 #pragma unroll
@@ -199,12 +258,12 @@ __global__ void __launch_bounds__(512, 1) step_tile_kernel(const __grid_constant
 #pragma unroll
           for (int m = 0; m < HALF; ++m) {
             const int o = gt + (h * HALF + m) * TE, r = o / Rb::NU, k = o - r * Rb::NU;
-            v[m] = (h * HALF + m < PER && o < TOT && k < Rb::NA) ? __ldg(arow + r * Rb::NA + k) : 0.0f;
+            v[m] = (h * HALF + m < PERS && o < TOT && k < Rb::NA) ? __ldg(arow + r * Rb::NA + k) : 0.0f;
           }
 #pragma unroll
           for (int m = 0; m < HALF; ++m) {
             const int o = gt + (h * HALF + m) * TE, r = o / Rb::NU, k = o - r * Rb::NU;
-            if (h * HALF + m < PER && o < TOT) {
+            if (h * HALF + m < PERS && o < TOT) {
               float c = v[m] * Rb::kActScale;
               const float hi = s_motor[2 * TC::NUP + k], lo = s_motor[TC::NUP + k];
               c = c > hi ? hi : c;
@@ -222,81 +281,92 @@ __global__ void __launch_bounds__(512, 1) step_tile_kernel(const __grid_constant
     }
     mbar_wait(bar, parity);
     parity ^= 1u;
-    TileIO<KIND, Rb> io{s_qp + gt * Rb::NQ, s_qv + gt * Rb::NV, s_co + gt * NCOMP};
+    TileIO<KIND, Rb> io;
+    io.qp = s_qp + gt * Rb::NQ;
+    io.qv = s_qv + gt * Rb::NV;
     StepOut so;
     env_step<KIND, Rb, TileIO<KIND, Rb>, TERMS>(io, p.cs, rows, st, contact, so);
-    s_guard[gt] = (so.reason == R_OBS_BOUNDS) ? 1 : 0;
     finish_env<KIND, Rb, TERMS, false>(p, env, st, so);
     const float ep_ret1 = ep_ret0 + so.raw_reward;
     if (p.ep_return) p.ep_return[env] = ep_ret1;
     if (STATS) {
-      a_sc[0] += 1.0;
-      a_sc[1] += so.reward;
-      a_sc[2] += double(so.reward) * so.reward;
-      if (so.done) {
-        a_sc[3] += 1.0;
-        a_sc[4] += ep_ret1;
-        a_sc[5] += st.ep_len;
-      }
+      float* xc = s_xc + gt * NXC;
+      xc[0] = 1.0f;
+      xc[1] = so.reward;
+      xc[2] = so.done ? 1.0f : 0.0f;
+      xc[3] = so.done ? ep_ret1 : 0.0f;
+      xc[4] = so.done ? float(st.ep_len) : 0.0f;
     }
-    group_sync(group);
-    // ---- observation: coalesced rows, joint blocks straight from the staged tiles -----------------------
-    float cs32[NCOLIT], css32[NCOLIT];
+    const bool guard = so.reason == R_OBS_BOUNDS;
+    // ---- observation tile in place: joint blocks -> registers, sync, finished rows over the input rows ----------
+    {
+      float jq[NJ], jv[NJ];
 #pragma unroll
-    for (int it = 0; it < NCOLIT; ++it) cs32[it] = css32[it] = 0.0f;
-#pragma unroll 2
-    for (int r = warp; r < TE; r += 4) {
-      const bool guard = s_guard[r] != 0;
-      float* orow = p.obs + (e0 + r) * DIM;
+      for (int j = 0; j < NJ; ++j) jq[j] = io.qp[7 + j];
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) jv[j] = io.qv[6 + j] * 0.1f;
+      group_sync(group);  // every input row of the tile is dead
+      float* orow = buf + gt * DIM;
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) orow[j] = guard ? 0.0f : jq[j];
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) orow[NJ + j] = guard ? 0.0f : jv[j];
+#pragma unroll
+      for (int j = 0; j < NCOMP; ++j) orow[2 * NJ + j] = guard ? 0.0f : io.co[j];
+    }
+    fence_async_smem();
+    group_sync(group);
+    if (gt == 0) {
+      tma_store_1d(p.obs + e0 * DIM, buf, sizeof(float) * TE * DIM);
+      bulk_commit();
+    }
+    if (tile + tstride < x.n_tiles) load_ahead(tile + tstride);
+    if (STATS) {  // column sums of the finished tile: lanes walk columns, the group's warps walk rows
+      float cs32[NCOLIT], css32[NCOLIT];
 #pragma unroll
       for (int it = 0; it < NCOLIT; ++it) {
+        cs32[it] = css32[it] = 0.0f;
         const int j = it * 32 + lane;
-        if (j < DIM) {
-          float v;
-          if (j < NJ) v = s_qp[r * Rb::NQ + 7 + j];
-          else if (j < 2 * NJ) v = s_qv[r * Rb::NV + 6 + (j - NJ)] * 0.1f;
-          else v = s_co[r * NCOMP + (j - 2 * NJ)];
-          if (guard) v = 0.0f;
-          orow[j] = v;
-          if (STATS) {
+        if (j < DIM + NXC) {
+          const float* src = j < DIM ? buf + warp * DIM + j : s_xc + warp * NXC + (j - DIM);
+          const int stride = 4 * (j < DIM ? DIM : NXC);
+#pragma unroll 8
+          for (int r = 0; r < TE / 4; ++r) {
+            const float v = src[r * stride];
             cs32[it] += v;
             css32[it] = fmaf(v, v, css32[it]);
           }
         }
       }
-    }
-    if (STATS) {
 #pragma unroll
       for (int it = 0; it < NCOLIT; ++it) {
-        a_cs[it] += cs32[it];
-        a_css[it] += css32[it];
+        my_acc[it * TE] += cs32[it];
+        my_acc[(NCOLIT + it) * TE] += css32[it];
       }
     }
-    group_sync(group);  // everyone is done reading the tile before the next TMA overwrites it
+    group_sync(group);  // everyone is done reading the tile before the next TMA load overwrites it
   }
+  if (gt == 0) bulk_wait_read0();  // shared memory stays valid until the last store has read it
 
   if (STATS && x.acc) {
-    // CTA-level reduction in shared memory (the tiles are dead by now), then ONE set of fp64 atomics per CTA
+    // CTA-level reduction of the shared-memory running sums, then ONE set of fp64 atomics per CTA
     __syncthreads();
-    double* sc = reinterpret_cast<double*>(s_table + (TABLE_SMEM ? x.table_floats : 0));  // [n_warps][2 * NCOLIT * 32 + 6]
-    constexpr int W = 2 * NCOLIT * 32 + 6;
-    const int wid = tid >> 5, n_warps = blockDim.x >> 5;
-#pragma unroll
-    for (int it = 0; it < NCOLIT; ++it) {
-      sc[wid * W + it * 32 + lane] = a_cs[it];
-      sc[wid * W + NCOLIT * 32 + it * 32 + lane] = a_css[it];
-    }
-#pragma unroll
-    for (int k = 0; k < 6; ++k) {
-      const double v = warp_sum(a_sc[k]);
-      if (lane == 0) sc[wid * W + 2 * NCOLIT * 32 + k] = v;
-    }
-    __syncthreads();
-    for (int j = tid; j < 2 * DIM + 6; j += blockDim.x) {
-      // j < 6: scalars; then sum obs[DIM]; then sum obs^2[DIM]
-      const int col = j < 6 ? 2 * NCOLIT * 32 + j : (j < 6 + DIM ? j - 6 : NCOLIT * 32 + (j - 6 - DIM));
+    const double* acc0 = reinterpret_cast<const double*>(s_groups + (size_t)n_groups * (TC::BUF_FLOATS + TC::XC_FLOATS));
+    auto colsum = [&](int c, int sq) {  // column c = it * 32 + lane, over every group and warp
+      const int it = c >> 5, ln = c & 31;
       double v = 0.0;
-      for (int w = 0; w < n_warps; ++w) v += sc[w * W + col];
+      for (int g = 0; g < n_groups; ++g)
+        for (int w = 0; w < 4; ++w) v += acc0[(size_t)g * 2 * NCOLIT * TE + ((sq ? NCOLIT : 0) + it) * TE + w * 32 + ln];
+      return v;
+    };
+    for (int j = tid; j < 2 * DIM + 6; j += blockDim.x) {
+      double v;
+      if (j == 0) v = colsum(DIM + 0, 0);        // count
+      else if (j == 1) v = colsum(DIM + 1, 0);   // sum r
+      else if (j == 2) v = colsum(DIM + 1, 1);   // sum r^2
+      else if (j < 6) v = colsum(DIM + j - 1, 0);  // n_done, sum ep_return(done), sum ep_len(done)
+      else if (j < 6 + DIM) v = colsum(j - 6, 0);
+      else v = colsum(j - 6 - DIM, 1);
       if (v != 0.0) atomicAdd(x.acc + j, v);
     }
   }

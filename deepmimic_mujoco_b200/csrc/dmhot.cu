@@ -3,6 +3,7 @@
 // tables, launches.  No CPU implementation of the step exists in this library.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -36,6 +37,7 @@ struct dm_handle {
   // bookkeeping
   long long launches = 0;
   int variant = -1;  // -1 auto
+  int table_smem_override = -1, max_groups_override = 0, l2_prefetch = 1;  // tuning knobs (DM_TABLE_SMEM, DM_MAX_GROUPS)
   bool timing = false;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev;
   size_t ev_used = 0;
@@ -89,6 +91,9 @@ extern "C" int dm_create(int device, int robot, int env_kind, dm_handle** out) {
   h->device = device;
   h->robot = robot;
   h->kind = env_kind;
+  if (const char* e = getenv("DM_TABLE_SMEM")) h->table_smem_override = atoi(e);
+  if (const char* e = getenv("DM_L2_PREFETCH")) h->l2_prefetch = atoi(e);
+  if (const char* e = getenv("DM_MAX_GROUPS")) h->max_groups_override = atoi(e);
   dispatch(h, [&](auto rb, auto kind) -> int {
     using Rb = decltype(rb);
     using OL = ObsLayout<decltype(kind)::value, Rb>;
@@ -264,24 +269,34 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
     p.obs = a->obs; p.reward = a->reward; p.done = a->done; p.reason = a->reason;
     p.torque = a->torque; p.terms = a->terms; p.ep_return = a->ep_return;
     p.cs = h->cs;
-    // K1b (shared-memory tiles + TMA bulk loads) for the full tiles of a row-major batch, K1a for the rest
-    const bool aligned = ((reinterpret_cast<uintptr_t>(a->qpos) | reinterpret_cast<uintptr_t>(a->qvel)) & 15u) == 0;
+    // K1b (shared-memory tiles, TMA in / TMA out) for the full 128-env tiles of a row-major batch, K1a for the rest
+    const bool aligned = ((reinterpret_cast<uintptr_t>(a->qpos) | reinterpret_cast<uintptr_t>(a->qvel) |
+                           reinterpret_cast<uintptr_t>(a->obs) | reinterpret_cast<uintptr_t>(a->action) |
+                           reinterpret_cast<uintptr_t>(a->torque)) & 15u) == 0;
     int tiled = 0;
     if (p.aos && h->variant != 0 && aligned && a->n >= TC::TE) tiled = a->n / TC::TE * TC::TE;
     timing_begin(h, s);
     if (tiled) {
       StepParams q = p;
       q.n = tiled;
+      constexpr int GMAX = KernelGroups<Rb>::G;
       const int n_tiles = tiled / TC::TE;
       const size_t table_bytes = sizeof(float) * (size_t)h->total_rows * RowLayout<Rb>::STRIDE;
-      const bool table_smem = TC::FIXED_BYTES + table_bytes + 2 * TC::GROUP_BYTES <= TC::SMEM_BUDGET;
-      int G = (int)((TC::SMEM_BUDGET - TC::FIXED_BYTES - (table_smem ? table_bytes : 0)) / TC::GROUP_BYTES);
-      G = G > TC::MAXG ? TC::MAXG : G;
+      const size_t per_group = TC::GROUP_BYTES + (a->accumulate_stats ? TC::ACC_BYTES : 0);
+      const int g_plain = (int)((TC::SMEM_BUDGET - TC::FIXED_BYTES) / per_group);
+      const int g_table = TC::FIXED_BYTES + table_bytes < TC::SMEM_BUDGET
+                              ? (int)((TC::SMEM_BUDGET - TC::FIXED_BYTES - table_bytes) / per_group) : 0;
+      // the clip table goes to shared memory when that does not cost a group of occupancy
+      bool table_smem = g_table >= (g_plain < GMAX ? g_plain : GMAX);
+      if (h->table_smem_override >= 0) table_smem = h->table_smem_override != 0 && g_table >= 1;
+      int G = table_smem ? g_table : g_plain;
+      G = G > GMAX ? GMAX : G;
+      if (h->max_groups_override > 0 && h->max_groups_override < G) G = h->max_groups_override;
       const int want = (n_tiles + h->num_sms - 1) / h->num_sms;  // spread small batches over all SMs first
       G = want < G ? (want < 1 ? 1 : want) : G;
       const int grid = (n_tiles + G - 1) / G < h->num_sms ? (n_tiles + G - 1) / G : h->num_sms;
-      const size_t smem = TC::FIXED_BYTES + (table_smem ? table_bytes : 0) + (size_t)G * TC::GROUP_BYTES;
-      TileExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float))};
+      const size_t smem = TC::FIXED_BYTES + (table_smem ? table_bytes : 0) + (size_t)G * per_group;
+      TileExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float)), h->l2_prefetch};
       auto launch = [&](auto kern) -> cudaError_t {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
@@ -290,7 +305,7 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
       };
       auto pick = [&](auto terms, auto stats) -> cudaError_t {
         constexpr bool T = decltype(terms)::value, S = decltype(stats)::value;
-        return table_smem ? launch(step_tile_kernel<KIND, Rb, T, S, true>) : launch(step_tile_kernel<KIND, Rb, T, S, false>);
+        return table_smem ? launch(step_tile_kernel<KIND, Rb, T, S, true, GMAX>) : launch(step_tile_kernel<KIND, Rb, T, S, false, GMAX>);
       };
       using std::true_type; using std::false_type;
       cudaError_t e = a->terms ? (a->accumulate_stats ? pick(true_type{}, true_type{}) : pick(true_type{}, false_type{}))
