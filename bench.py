@@ -264,20 +264,26 @@ def e2e_region(args, steps, warmup, seed):
     B = 8
     s = synth_states(env.hp, args.envs, B, seed + 1, dev)
     host = {k: v.cpu().numpy() for k, v in s.items()}
+    host["contact"] = host["contact"].astype(np.uint32)
     env.reset()
-    for i in range(warmup):
+
+    def one(i):
         b = i % B
-        env.step(host["action"][b], force_state=(host["qpos"][b], host["qvel"][b], host["contact"][b].astype(np.uint32)))
+        return env.step(host["action"][b], force_state=(host["qpos"][b], host["qvel"][b], host["contact"][b]))
+
+    for i in range(warmup):
+        one(i)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for i in range(steps):
-        b = i % B
-        env.step(host["action"][b], force_state=(host["qpos"][b], host["qvel"][b], host["contact"][b].astype(np.uint32)))
+        obs, rew, done, infos = one(i)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
+    assert obs.shape == (args.envs, env.hp.obs_dim) and len(infos) == args.envs
     out = dict(value=args.envs * steps / dt, unit="env-steps/s", h2d_bytes_per_step=int(env.h2d_bytes),
                d2h_bytes_per_step=int(env.d2h_bytes), ms_per_step=1e3 * dt / steps,
-               api="DPVecEnv.step(actions, force_state=(qpos, qvel, contact)) -> dm_step_host")
+               api="DPVecEnv.step(actions, force_state=(qpos, qvel, contact)) with ordinary (pageable) numpy inputs and copied "
+                   "outputs: copy into the handle's pinned buffers, one H2D, kernel, one D2H (dm_step_host)")
     env.close()
     return out
 

@@ -52,7 +52,7 @@ class ResetArgs(C.Structure):
 
 # every symbol include/dmhot.h declares (tests check that the library exports each one)
 SYMBOLS = ["dm_abi_version", "dm_create", "dm_destroy", "dm_last_error", "dm_get_dims", "dm_get_model", "dm_fk_tables",
-           "dm_upload_clips", "dm_get_packed_rows", "dm_step", "dm_reset", "dm_step_host", "dm_reset_host",
+           "dm_upload_clips", "dm_get_packed_rows", "dm_step", "dm_reset", "dm_step_host", "dm_reset_host", "dm_host_buffers",
            "dm_stats_zero", "dm_stats_device_ptr", "dm_stats_read", "dm_launch_count", "dm_step_kernel_time",
            "dm_set_timing", "dm_set_kernel_variant"]
 
@@ -81,6 +81,7 @@ def lib():
     L.dm_reset.argtypes = [C.c_void_p, C.POINTER(ResetArgs)]
     L.dm_step_host.argtypes = [C.c_void_p, C.POINTER(StepArgs), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.dm_reset_host.argtypes = [C.c_void_p, C.POINTER(ResetArgs)]
+    L.dm_host_buffers.argtypes = [C.c_void_p, C.c_int32, C.POINTER(StepArgs)]
     L.dm_stats_zero.argtypes = [C.c_void_p, C.c_void_p]
     L.dm_stats_device_ptr.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int32)]
     L.dm_stats_read.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]

@@ -112,7 +112,7 @@ struct TileIO {
 
 // groups per CTA the kernel is compiled for (register budget = 65536 / (128 G) per thread)
 template <class Rb>
-struct KernelGroups {
+struct KernelGroups {  // measured on humanoid3d: G = 5 (96 registers, ~330 B of spills) is 40 % slower than G = 4
   static constexpr int G = 4;
 };
 template <>
@@ -231,11 +231,14 @@ __global__ void __launch_bounds__(128 * G, 1) step_tile_kernel(const __grid_cons
     if (p.torque) {
       if (kVecTorque) {  // 128-bit path: chunk c covers actuators 4 (c mod NA/4) .. + 3; loaded a tile ahead
         float4* t4 = reinterpret_cast<float4*>(p.torque + e0 * Rb::NU);
+        const int r4 = gt % K4;  // (gt + m TE) mod K4 from one remainder: nothing per-m to keep live (or spill)
 #pragma unroll
         for (int m = 0; m < PER; ++m) {
           const int c = gt + m * TE;
           if (c < CH) {
-            const int k0 = (c % K4) * 4;
+            int km = r4 + (m * TE) % K4;
+            km -= km >= K4 ? K4 : 0;
+            const int k0 = km * 4;
             const float4 g = *reinterpret_cast<const float4*>(s_motor + k0);
             const float4 lo = *reinterpret_cast<const float4*>(s_motor + TC::NUP + k0);
             const float4 hi = *reinterpret_cast<const float4*>(s_motor + 2 * TC::NUP + k0);

@@ -17,6 +17,12 @@ using namespace dm;
 
 static thread_local std::string g_last_error;
 
+struct Stage {  // one pinned host area + its device mirror
+  void* h_pin = nullptr;
+  void* d_mem = nullptr;
+  size_t bytes = 0;
+};
+
 struct dm_handle {
   int device = 0, robot = 0, kind = 0, num_sms = 148;
   dm_dims_t dims{};
@@ -29,10 +35,8 @@ struct dm_handle {
   ClipSet cs{};
   // statistics
   double* d_stats = nullptr;
-  // host-mode staging
-  void* h_pin = nullptr;
-  void* d_stage = nullptr;
-  size_t stage_bytes = 0;
+  // host-mode staging (the step's area doubles as the caller-visible pinned buffers of dm_host_buffers)
+  Stage step_stage, reset_stage;
   cudaStream_t host_stream = nullptr;
   // bookkeeping
   long long launches = 0;
@@ -120,8 +124,10 @@ extern "C" int dm_destroy(dm_handle* h) {
   cudaFree(h->d_rows);
   cudaFree(h->d_state_rows);
   cudaFree(h->d_stats);
-  cudaFree(h->d_stage);
-  if (h->h_pin) cudaFreeHost(h->h_pin);
+  for (Stage* st : {&h->step_stage, &h->reset_stage}) {
+    cudaFree(st->d_mem);
+    if (st->h_pin) cudaFreeHost(st->h_pin);
+  }
   for (auto& p : h->ev) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
   if (h->host_stream) cudaStreamDestroy(h->host_stream);
   delete h;
@@ -388,16 +394,16 @@ extern "C" int dm_reset(dm_handle* h, const dm_reset_args* a) {
 }
 
 // ---- host-buffer variants ---------------------------------------------------------------------
-static int ensure_stage(dm_handle* h, size_t bytes) {
-  if (bytes <= h->stage_bytes) return DM_OK;
-  cudaFree(h->d_stage);
-  if (h->h_pin) cudaFreeHost(h->h_pin);
-  h->d_stage = h->h_pin = nullptr;
-  h->stage_bytes = 0;
-  const size_t cap = bytes + bytes / 4 + 4096;
-  CU(h, cudaMalloc(&h->d_stage, cap));
-  CU(h, cudaMallocHost(&h->h_pin, cap));
-  h->stage_bytes = cap;
+static int ensure_stage(dm_handle* h, Stage& st, size_t bytes) {
+  if (bytes <= st.bytes) return DM_OK;
+  cudaFree(st.d_mem);
+  if (st.h_pin) cudaFreeHost(st.h_pin);
+  st.d_mem = st.h_pin = nullptr;
+  st.bytes = 0;
+  const size_t cap = bytes + 4096;
+  CU(h, cudaMalloc(&st.d_mem, cap));
+  CU(h, cudaMallocHost(&st.h_pin, cap));
+  st.bytes = cap;
   return DM_OK;
 }
 
@@ -414,6 +420,56 @@ struct Carver {  // lays buffers out back to back (256-byte aligned) in the pinn
   }
 };
 
+// Staging layout of one host-buffer step: [inputs | in-out state | outputs], so that the H2D copy
+// (inputs + state) and the D2H copy (state + outputs) are ONE contiguous transfer each.
+struct StepStage {
+  float *hq, *dq, *hv, *dv, *ha, *da;            // qpos qvel action
+  uint32_t *hc, *dc;                             // contact
+  int32_t *hi, *di, *hl, *dl, *hk, *dk;          // idx ep_len clip   (in-out)
+  float *her, *der;                              // ep_return         (in-out)
+  float *ho, *dob, *hr, *dr, *ht, *dt, *hm, *dmt;  // obs reward torque terms
+  uint8_t *hd, *dd, *hz, *dz;                    // done reason
+  size_t state0, out0, end;
+};
+
+static size_t step_stage_bytes(const dm_dims_t& d, size_t n) {
+  return n * (sizeof(float) * (d.nq + d.nv + d.na + d.obs_dim + 1 + d.nu + DM_NTERMS + 1) + 4 * 4 + 2) + 16 * 256;
+}
+
+static StepStage carve_step(const dm_handle* h, size_t n) {
+  const dm_dims_t& d = h->dims;
+  Carver c{(char*)h->step_stage.h_pin, (char*)h->step_stage.d_mem};
+  StepStage s;
+  c.take(n * d.nq, &s.hq, &s.dq); c.take(n * d.nv, &s.hv, &s.dv); c.take(n * d.na, &s.ha, &s.da); c.take(n, &s.hc, &s.dc);
+  c.off = (c.off + 255) & ~size_t(255);
+  s.state0 = c.off;
+  c.take(n, &s.hi, &s.di); c.take(n, &s.hl, &s.dl); c.take(n, &s.hk, &s.dk); c.take(n, &s.her, &s.der);
+  c.off = (c.off + 255) & ~size_t(255);
+  s.out0 = c.off;
+  c.take(n * d.obs_dim, &s.ho, &s.dob); c.take(n, &s.hr, &s.dr); c.take(n * d.nu, &s.ht, &s.dt);
+  c.take(n * DM_NTERMS, &s.hm, &s.dmt); c.take(n, &s.hd, &s.dd); c.take(n, &s.hz, &s.dz);
+  s.end = c.off;
+  return s;
+}
+
+// Pinned host buffers for n environments, laid out exactly as dm_step_host stages them.  A caller that keeps its
+// per-step arrays HERE (and passes these very pointers) gets zero staging copies: dm_step_host then issues one
+// H2D transfer, the kernel, and one D2H transfer.  The pointers stay valid until dm_host_buffers / dm_step_host is
+// called with a larger n, or the handle is destroyed.
+extern "C" int dm_host_buffers(dm_handle* h, int32_t n, dm_step_args* out) {
+  if (!h || !out || n <= 0) return fail(h, DM_E_ARG, "dm_host_buffers: bad argument");
+  CU(h, cudaSetDevice(h->device));
+  int rc = ensure_stage(h, h->step_stage, step_stage_bytes(h->dims, (size_t)n));
+  if (rc) return rc;
+  const StepStage s = carve_step(h, (size_t)n);
+  memset(out, 0, sizeof *out);
+  out->n = n; out->layout = DM_LAYOUT_AOS; out->ld = 0;
+  out->qpos = s.hq; out->qvel = s.hv; out->action = s.ha; out->contact = s.hc;
+  out->idx = s.hi; out->ep_len = s.hl; out->clip = s.hk; out->ep_return = s.her;
+  out->obs = s.ho; out->reward = s.hr; out->torque = s.ht; out->terms = s.hm; out->done = s.hd; out->reason = s.hz;
+  return DM_OK;
+}
+
 extern "C" int dm_step_host(dm_handle* h, const dm_step_args* a, int64_t* h2d_bytes, int64_t* d2h_bytes) {
   int rc = check_step_args(h, a, "dm_step_host");
   if (rc) return rc;
@@ -422,57 +478,45 @@ extern "C" int dm_step_host(dm_handle* h, const dm_step_args* a, int64_t* h2d_by
   const dm_dims_t& d = h->dims;
   const size_t n = a->n;
   if (n == 0) return DM_OK;
-  const size_t need = n * (sizeof(float) * (d.nq + d.nv + d.na + d.obs_dim + 1 + d.nu + DM_NTERMS + 1) + 4 * 4 + 2) + 16 * 256;
-  rc = ensure_stage(h, need);
+  rc = ensure_stage(h, h->step_stage, step_stage_bytes(d, n));
   if (rc) return rc;
-  Carver c{(char*)h->h_pin, (char*)h->d_stage};
+  const StepStage g = carve_step(h, n);
   cudaStream_t s = h->host_stream;
-  // inputs are contiguous in the staging area: one H2D copy
-  float *hq, *dq, *hv, *dv, *ha, *da, *her, *der;
-  uint32_t *hc, *dc;
-  int32_t *hi, *di, *hl, *dl, *hk, *dk;
-  c.take(n * d.nq, &hq, &dq); c.take(n * d.nv, &hv, &dv); c.take(n * d.na, &ha, &da);
-  c.take(n, &hc, &dc); c.take(n, &hi, &di); c.take(n, &hl, &dl); c.take(n, &hk, &dk); c.take(n, &her, &der);
-  const size_t in_bytes = c.off;
-  memcpy(hq, a->qpos, sizeof(float) * n * d.nq);
-  memcpy(hv, a->qvel, sizeof(float) * n * d.nv);
-  memcpy(ha, a->action, sizeof(float) * n * d.na);
-  if (a->contact) memcpy(hc, a->contact, 4 * n); else memset(hc, 0, 4 * n);
-  memcpy(hi, a->idx, 4 * n);
-  memcpy(hl, a->ep_len, 4 * n);
-  if (a->clip) memcpy(hk, a->clip, 4 * n); else memset(hk, 0, 4 * n);
-  if (a->ep_return) memcpy(her, a->ep_return, 4 * n);
-  CU(h, cudaMemcpyAsync(h->d_stage, h->h_pin, in_bytes, cudaMemcpyHostToDevice, s));
-  // outputs, again contiguous: one D2H copy (plus the state ints living in the input block)
-  c.off = (c.off + 255) & ~size_t(255);
-  const size_t out0 = c.off;
-  float *ho, *dob, *hr, *dr, *ht, *dt, *hm, *dm_;
-  uint8_t *hd, *dd, *hz, *dz;
-  c.take(n * d.obs_dim, &ho, &dob); c.take(n, &hr, &dr); c.take(n * d.nu, &ht, &dt); c.take(n * DM_NTERMS, &hm, &dm_);
-  c.take(n, &hd, &dd); c.take(n, &hz, &dz);
-  const size_t out_bytes = c.off - out0;
+  // a buffer that already IS its staging slot (dm_host_buffers) needs no copy
+  auto in = [](void* slot, const void* src, size_t bytes) { if (src != slot) { if (src) memcpy(slot, src, bytes); else memset(slot, 0, bytes); } };
+  auto out = [](void* dst, const void* slot, size_t bytes) { if (dst && dst != slot) memcpy(dst, slot, bytes); };
+  in(g.hq, a->qpos, sizeof(float) * n * d.nq);
+  in(g.hv, a->qvel, sizeof(float) * n * d.nv);
+  in(g.ha, a->action, sizeof(float) * n * d.na);
+  in(g.hc, a->contact, 4 * n);
+  in(g.hi, a->idx, 4 * n);
+  in(g.hl, a->ep_len, 4 * n);
+  in(g.hk, a->clip, 4 * n);
+  if (a->ep_return) in(g.her, a->ep_return, 4 * n);
+  const size_t in_bytes = g.out0;  // inputs + in-out state
+  CU(h, cudaMemcpyAsync(h->step_stage.d_mem, h->step_stage.h_pin, in_bytes, cudaMemcpyHostToDevice, s));
   dm_step_args k = *a;
-  k.qpos = dq; k.qvel = dv; k.action = da; k.contact = dc; k.idx = di; k.ep_len = dl; k.clip = dk;
-  k.obs = dob; k.reward = dr; k.done = dd; k.reason = dz; k.torque = a->torque ? dt : nullptr;
-  k.terms = a->terms ? dm_ : nullptr; k.ep_return = a->ep_return ? der : nullptr;
+  k.qpos = g.dq; k.qvel = g.dv; k.action = g.da; k.contact = g.dc; k.idx = g.di; k.ep_len = g.dl; k.clip = g.dk;
+  k.obs = g.dob; k.reward = g.dr; k.done = g.dd; k.reason = g.dz; k.torque = a->torque ? g.dt : nullptr;
+  k.terms = a->terms ? g.dmt : nullptr; k.ep_return = a->ep_return ? g.der : nullptr;
   rc = launch_step(h, &k, s);
   if (rc) return rc;
-  CU(h, cudaMemcpyAsync((char*)h->h_pin + out0, (char*)h->d_stage + out0, out_bytes, cudaMemcpyDeviceToHost, s));
-  const size_t st0 = (char*)hi - (char*)h->h_pin, st_bytes = (char*)(her + n) - (char*)hi;
-  CU(h, cudaMemcpyAsync((char*)h->h_pin + st0, (char*)h->d_stage + st0, st_bytes, cudaMemcpyDeviceToHost, s));
+  const size_t back_bytes = g.end - g.state0;  // in-out state + outputs
+  CU(h, cudaMemcpyAsync((char*)h->step_stage.h_pin + g.state0, (char*)h->step_stage.d_mem + g.state0, back_bytes,
+                        cudaMemcpyDeviceToHost, s));
   CU(h, cudaStreamSynchronize(s));
-  memcpy(a->obs, ho, sizeof(float) * n * d.obs_dim);
-  memcpy(a->reward, hr, 4 * n);
-  memcpy(a->done, hd, n);
-  if (a->reason) memcpy(a->reason, hz, n);
-  if (a->torque) memcpy(a->torque, ht, sizeof(float) * n * d.nu);
-  if (a->terms) memcpy(a->terms, hm, sizeof(float) * n * DM_NTERMS);
-  memcpy(a->idx, hi, 4 * n);
-  memcpy(a->ep_len, hl, 4 * n);
-  if (a->clip) memcpy(a->clip, hk, 4 * n);
-  if (a->ep_return) memcpy(a->ep_return, her, 4 * n);
+  out(a->obs, g.ho, sizeof(float) * n * d.obs_dim);
+  out(a->reward, g.hr, 4 * n);
+  out(a->done, g.hd, n);
+  out(a->reason, g.hz, n);
+  out(a->torque, g.ht, sizeof(float) * n * d.nu);
+  out(a->terms, g.hm, sizeof(float) * n * DM_NTERMS);
+  out(a->idx, g.hi, 4 * n);
+  out(a->ep_len, g.hl, 4 * n);
+  out(a->clip, g.hk, 4 * n);
+  out(a->ep_return, g.her, 4 * n);
   if (h2d_bytes) *h2d_bytes = (int64_t)in_bytes;
-  if (d2h_bytes) *d2h_bytes = (int64_t)(out_bytes + st_bytes);
+  if (d2h_bytes) *d2h_bytes = (int64_t)back_bytes;
   return DM_OK;
 }
 
@@ -484,9 +528,9 @@ extern "C" int dm_reset_host(dm_handle* h, const dm_reset_args* a) {
   const dm_dims_t& d = h->dims;
   const size_t n = a->n;
   if (n == 0) return DM_OK;
-  rc = ensure_stage(h, n * (sizeof(float) * (d.nq + d.nv + 2 * d.obs_dim + 1) + 4 * 6 + 1) + 16 * 256);
+  rc = ensure_stage(h, h->reset_stage, n * (sizeof(float) * (d.nq + d.nv + 2 * d.obs_dim + 1) + 4 * 6 + 1) + 16 * 256);
   if (rc) return rc;
-  Carver c{(char*)h->h_pin, (char*)h->d_stage};
+  Carver c{(char*)h->reset_stage.h_pin, (char*)h->reset_stage.d_mem};
   cudaStream_t s = h->host_stream;
   uint8_t *hm, *dmk;
   int32_t *hf, *df, *hco, *dco, *hi, *di, *hl, *dl, *hk, *dk;
@@ -508,13 +552,13 @@ extern "C" int dm_reset_host(dm_handle* h, const dm_reset_args* a) {
   if (a->qpos) memcpy(hq, a->qpos, sizeof(float) * n * d.nq);
   if (a->qvel) memcpy(hv, a->qvel, sizeof(float) * n * d.nv);
   memcpy(ho, a->obs, sizeof(float) * n * d.obs_dim);
-  CU(h, cudaMemcpyAsync(h->d_stage, h->h_pin, c.off, cudaMemcpyHostToDevice, s));
+  CU(h, cudaMemcpyAsync(h->reset_stage.d_mem, h->reset_stage.h_pin, c.off, cudaMemcpyHostToDevice, s));
   dm_reset_args k = *a;
   k.mask = dmk; k.frame = a->frame ? df : nullptr; k.coin = a->coin ? dco : nullptr; k.contact = dc;
   k.idx = di; k.ep_len = dl; k.clip = dk; k.ep_return = der; k.qpos = dq; k.qvel = dv; k.obs = dob; k.terminal_obs = a->terminal_obs ? dto : nullptr;
   rc = launch_reset(h, &k, s);
   if (rc) return rc;
-  CU(h, cudaMemcpyAsync(h->h_pin, h->d_stage, c.off, cudaMemcpyDeviceToHost, s));
+  CU(h, cudaMemcpyAsync(h->reset_stage.h_pin, h->reset_stage.d_mem, c.off, cudaMemcpyDeviceToHost, s));
   CU(h, cudaStreamSynchronize(s));
   memcpy(a->idx, hi, 4 * n);
   memcpy(a->ep_len, hl, 4 * n);

@@ -178,6 +178,30 @@ class HotPath:
         N.check(self.L.dm_step_host(self.h, C.byref(a), C.byref(hb), C.byref(db)), self.h, "dm_step_host")
         return hb.value, db.value
 
+    def host_buffers(self, n, terms=False):
+        """Pinned host arrays (numpy views of memory owned by the handle) laid out as dm_step_host stages them.
+        Passing exactly these arrays to step_host() makes the step zero-copy on the host: one H2D transfer, the
+        kernel, one D2H transfer.  Valid until host_buffers / step_host is called with a larger n, or close()."""
+        a = N.StepArgs()
+        N.check(self.L.dm_host_buffers(self.h, int(n), C.byref(a)), self.h, "dm_host_buffers")
+        d = self.dims
+
+        def view(ptr, shape, ctype, dtype):
+            cnt = int(np.prod(shape))
+            arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(ctype)), shape=(cnt,))
+            return arr.view(dtype).reshape(shape)
+
+        f, i32, u32, u8 = (C.c_float, np.float32), (C.c_int32, np.int32), (C.c_uint32, np.uint32), (C.c_uint8, np.uint8)
+        spec = dict(qpos=((n, d.nq), f), qvel=((n, d.nv), f), action=((n, d.na), f), contact=((n,), u32),
+                    idx=((n,), i32), ep_len=((n,), i32), clip=((n,), i32), ep_return=((n,), f),
+                    obs=((n, d.obs_dim), f), reward=((n,), f), torque=((n, d.nu), f), done=((n,), u8), reason=((n,), u8))
+        if terms:
+            spec["terms"] = ((n, N.NTERMS), f)
+        out = {k: view(getattr(a, k), shape, ct, dt) for k, (shape, (ct, dt)) in spec.items()}
+        for v in out.values():
+            v[...] = 0
+        return out
+
     def _reset_args(self, n, mask, frame, coin, contact, qpos, qvel, idx, ep_len, clip, obs, ep_return, soa_ld, seed,
                     counter, stream, terminal_obs=None):
         a = N.ResetArgs()

@@ -46,9 +46,33 @@ class Box:
         return x.shape == self.shape and bool(np.all(x >= self.low) and np.all(x <= self.high))
 
 
+class LazyInfos(list):
+    """The `infos` list of a VecEnv step: a real list of num_envs per-env dicts whose entries are created on first
+    access.  Building num_envs empty dicts eagerly costs more than the whole GPU step at 4096 environments."""
+
+    def __init__(self, n):
+        super().__init__([None] * n)
+
+    def __getitem__(self, i):
+        v = list.__getitem__(self, i)
+        if isinstance(i, slice):
+            return [self[j] for j in range(*i.indices(len(self)))]
+        if v is None:
+            v = {}
+            list.__setitem__(self, i, v)
+        return v
+
+    def __iter__(self):
+        for i in range(len(self)):
+            yield self[i]
+
+    def __eq__(self, other):
+        return list(iter(self)) == list(other)
+
+
 class DPVecEnv:
     def __init__(self, num_envs, motion="walk", robot="humanoid3d", combined=False, device=0, seed=0, physics=None,
-                 info_terms=False):
+                 info_terms=False, copy_outputs=True):
         self.num_envs = int(num_envs)
         self.robot = "unitree_g1" if combined else robot
         self.combined = bool(combined)
@@ -71,24 +95,32 @@ class DPVecEnv:
         self.observation_space = Box(np.full(d.obs_dim, -np.inf), np.full(d.obs_dim, np.inf))
         n = self.num_envs
         self._seed, self._counter = int(seed), 0
-        # host-side per-env state (the reference keeps these as Python attributes of each env)
-        self.idx = np.zeros(n, np.int32)       # idx_curr / current_motion_n_steps
-        self.ep_len = np.zeros(n, np.int32)    # episode_length
-        self.clip = np.zeros(n, np.int32)      # clip id / motion state
-        self.ep_return = np.zeros(n, np.float32)
-        self.qpos = np.zeros((n, d.nq), np.float32)
-        self.qvel = np.zeros((n, d.nv), np.float32)
-        self.obs = np.zeros((n, d.obs_dim), np.float32)
-        self.reward = np.zeros(n, np.float32)
-        self.done = np.zeros(n, np.uint8)
-        self.reason = np.zeros(n, np.uint8)
-        self.torque = np.zeros((n, d.nu), np.float32)
-        self.terms = np.zeros((n, N.NTERMS), np.float32) if info_terms else None
+        self.copy_outputs = bool(copy_outputs)
+        # Per-env state and the step's input / output arrays live in PINNED host memory owned by the handle, laid
+        # out as dm_step_host stages them: a step is one H2D transfer, the kernel, one D2H transfer, no staging
+        # copies.  (The reference keeps these as Python attributes of each env process.)
+        pin = self.hp.host_buffers(n, terms=info_terms)
+        self._pin = pin
+        self.idx = pin["idx"]              # idx_curr / current_motion_n_steps
+        self.ep_len = pin["ep_len"]        # episode_length
+        self.clip = pin["clip"]            # clip id / motion state
+        self.ep_return = pin["ep_return"]
+        self.qpos, self.qvel = pin["qpos"], pin["qvel"]
+        self.obs, self.reward, self.done, self.reason = pin["obs"], pin["reward"], pin["done"], pin["reason"]
+        self.torque = pin["torque"]
+        self.terms = pin.get("terms")
         self.terminal_obs = np.zeros((n, d.obs_dim), np.float32)
         self._actions = None
         self._force = None
         self.h2d_bytes = self.d2h_bytes = 0
         self._dev = None
+
+    def input_buffers(self):
+        """The pinned (qpos, qvel, contact, action) arrays of the next step.  A simulator that writes its
+        post-physics state straight into them and then calls step(actions_view, force_state=(qpos, qvel, contact))
+        with these very arrays skips every host-side copy."""
+        p = self._pin
+        return p["qpos"], p["qvel"], p["contact"], p["action"]
 
     # ------------------------------------------------------------------ VecEnv surface
     def set_clips(self, clip_ids):
@@ -110,54 +142,62 @@ class DPVecEnv:
         return self.obs.copy()
 
     def step_async(self, actions, force_state=None):
-        self._actions = np.ascontiguousarray(actions, dtype=np.float32)
-        assert self._actions.shape == (self.num_envs, self.hp.na), "actions must be [num_envs, %d]" % self.hp.na
+        actions = np.asarray(actions)
+        assert actions.shape == (self.num_envs, self.hp.na), "actions must be [num_envs, %d]" % self.hp.na
+        self._actions = self._into(self._pin["action"], actions)
         self._force = force_state
+
+    @staticmethod
+    def _into(dst, src):
+        """src -> the pinned array dst (no-op when the caller already wrote into dst)."""
+        if src is not dst:
+            np.copyto(dst, src, casting="unsafe")
+        return dst
 
     def step_wait(self):
         n = self.num_envs
+        p = self._pin
         contact = None
         if self._force is not None:
-            qpos = np.ascontiguousarray(self._force[0], dtype=np.float32)
-            qvel = np.ascontiguousarray(self._force[1], dtype=np.float32)
-            if len(self._force) > 2 and self._force[2] is not None:
-                contact = np.ascontiguousarray(self._force[2], dtype=np.uint32)
+            fs = self._force
         elif self.physics is not None:
-            # torque of the previous action is not known before the kernel ran: compute it on the host the way
-            # MuJoCo would (gear * clip(scale * a, ctrlrange)) is the kernel's job, so physics gets the action
-            qpos, qvel, contact = self.physics(self.qpos, self.qvel, self._actions)
-            qpos = np.ascontiguousarray(qpos, dtype=np.float32)
-            qvel = np.ascontiguousarray(qvel, dtype=np.float32)
-            contact = None if contact is None else np.ascontiguousarray(contact, dtype=np.uint32)
+            # the torque belongs to the kernel (gear * clip(scale * a, ctrlrange)), so physics gets the action
+            fs = self.physics(self.qpos, self.qvel, self._actions)
         else:
             raise N.DmError("DPVecEnv.step needs force_state=(qpos, qvel[, contact]) or a physics callback: MuJoCo's "
                             "mj_step is outside this package")
-        assert qpos.shape == self.qpos.shape and qvel.shape == self.qvel.shape
-        self.qpos, self.qvel = qpos.copy(), qvel.copy()
+        assert np.shape(fs[0]) == p["qpos"].shape and np.shape(fs[1]) == p["qvel"].shape
+        self.qpos, self.qvel = self._into(p["qpos"], fs[0]), self._into(p["qvel"], fs[1])
+        if len(fs) > 2 and fs[2] is not None:
+            contact = self._into(p["contact"], fs[2])
         h2d, d2h = self.hp.step_host(n, self.qpos, self.qvel, self._actions, contact, self.idx, self.ep_len, self.clip,
                                      self.obs, self.reward, self.done, self.reason, self.torque, self.terms, self.ep_return)
         self.h2d_bytes, self.d2h_bytes = h2d, d2h
-        dones = self.done.astype(bool)
-        rews = self.reward.copy()
-        infos = [{} for _ in range(n)]
+        dones = self.done.view(np.bool_)
+        infos = LazyInfos(n)
         if self.info_terms:
             for i in range(n):
                 if self.reason[i] != 8:
                     infos[i].update({k: float(self.terms[i, j]) for j, k in enumerate(N.TERM_NAMES[:5])})
+        rews = self.reward.copy() if self.copy_outputs else self.reward
         if dones.any():
+            dones = dones.copy()
             ids = np.nonzero(dones)[0]
             ep_ret, ep_len, reasons = self.ep_return[ids].copy(), self.ep_len[ids].copy(), self.reason[ids].copy()
             self.terminal_obs[ids] = self.obs[ids]
             self._counter += 1
-            self.hp.reset_host(n, self.idx, self.ep_len, self.clip, self.obs, mask=self.done, qpos=self.qpos,
+            self.hp.reset_host(n, self.idx, self.ep_len, self.clip, self.obs, mask=dones.view(np.uint8), qpos=self.qpos,
                                qvel=self.qvel, ep_return=self.ep_return, seed=self._seed, counter=self._counter)
             for k, i in enumerate(ids):
-                infos[i]["terminal_observation"] = self.terminal_obs[i].copy()
-                infos[i]["TimeLimit.truncated"] = bool(reasons[k] == 5)
+                info = infos[i]
+                info["terminal_observation"] = self.terminal_obs[i].copy()
+                info["TimeLimit.truncated"] = bool(reasons[k] == 5)
                 if reasons[k] not in (0, 8):
-                    infos[i]["done_reason"] = N.DONE_REASONS[reasons[k]]
-                infos[i]["episode"] = {"r": float(ep_ret[k]), "l": int(ep_len[k])}
-        return self.obs.copy(), rews, dones, infos
+                    info["done_reason"] = N.DONE_REASONS[reasons[k]]
+                info["episode"] = {"r": float(ep_ret[k]), "l": int(ep_len[k])}
+        elif self.copy_outputs:
+            dones = dones.copy()
+        return (self.obs.copy() if self.copy_outputs else self.obs), rews, dones, infos
 
     def step(self, actions, force_state=None):
         self.step_async(actions, force_state)

@@ -155,6 +155,12 @@ int dm_reset(dm_handle* h, const dm_reset_args* a);
  * receive the bytes moved. */
 int dm_step_host(dm_handle* h, const dm_step_args* a, int64_t* h2d_bytes, int64_t* d2h_bytes);
 int dm_reset_host(dm_handle* h, const dm_reset_args* a);
+/* Pinned host buffers for n environments, laid out exactly as dm_step_host stages them: every pointer field of
+ * *out (qpos ... reason, incl. torque / terms / ep_return) receives a HOST pointer owned by the handle.  A caller
+ * that keeps its per-step arrays there and passes those very pointers to dm_step_host pays no staging copies --
+ * one H2D transfer, the kernel, one D2H transfer.  (The reference's SubprocVecEnv pickles every observation
+ * through a pipe instead, src/sb3_ppo.py:275-278.)  Valid until a call with a larger n or dm_destroy. */
+int dm_host_buffers(dm_handle* h, int32_t n, dm_step_args* out);
 
 /* reward / observation-normaliser statistics (new functionality, no reference counterpart):
  * [count, sum r, sum r^2, n_done, sum ep_return(done), sum ep_len(done), sum obs[D], sum obs^2[D]] */

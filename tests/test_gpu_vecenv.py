@@ -1,0 +1,148 @@
+"""The reference-facing Python surface on the GPU: DPVecEnv (SB3 VecEnv convention: auto-reset,
+terminal_observation, infos), its pinned zero-copy inputs, and the single-env DPEnv / DPCombinedEnv mirrors,
+all against the float64 oracle on the same seeded inputs.  Tolerance: 1e-5 relative (north_star), written as
+|a - b| <= 1e-5 * max(|b|, 0.05); done flags, indices and counters bit-exact."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+RTOL, ATOL = 1e-5, 5e-7
+
+
+def _states(env_or, rng, n, sig=1.0):
+    """clip frame + Gaussian perturbation; a few envs are pushed below low_z so that they terminate."""
+    m = env_or.mocap
+    nq, nv = env_or.model.nq, env_or.model.nv
+    f = rng.integers(0, m.get_length(), n)
+    q = np.asarray(m.data_config)[f] + sig * np.concatenate([rng.normal(0, 0.02, (n, 7)), rng.normal(0, 0.05, (n, nq - 7))], 1)
+    v = np.asarray(m.data_vel)[f] + sig * rng.normal(0, 0.5, (n, nv))
+    q[::7, 2] -= 0.6  # fallen
+    return q.astype(np.float32), v.astype(np.float32)
+
+
+def test_vecenv_matches_oracle_with_autoreset():
+    from deepmimic_mujoco_b200.vec_env import DPVecEnv, LazyInfos
+    from oracle.envs import SingleClipEnv
+    n, steps = 96, 4
+    rng = np.random.default_rng(5)
+    env = DPVecEnv(n, motion="walk", robot="humanoid3d", seed=11)
+    frames = rng.integers(0, 76, n).astype(np.int32)
+    obs = env.reset(frame=frames)
+    ors = [SingleClipEnv("walk", "humanoid3d") for _ in range(n)]
+    want = np.stack([o.reset(int(f)) for o, f in zip(ors, frames)])
+    np.testing.assert_allclose(obs, want, rtol=RTOL, atol=ATOL)
+    n_done = 0
+    for t in range(steps):
+        q, v = _states(ors[0], rng, n)
+        contact = rng.integers(0, 4, n).astype(np.uint32)
+        act = rng.uniform(-2, 2, (n, 28)).astype(np.float32)
+        obs, rew, done, infos = env.step(act, force_state=(q, v, contact))
+        assert isinstance(infos, list) and isinstance(infos, LazyInfos) and len(infos) == n
+        assert obs.dtype == np.float32 and done.dtype == np.bool_
+        for i, o in enumerate(ors):
+            wo, wr, wd, wi = o.step(act[i].astype(np.float64), (q[i].astype(np.float64), v[i].astype(np.float64)), int(contact[i]))
+            assert bool(done[i]) == bool(wd), (t, i)
+            np.testing.assert_allclose(rew[i], wr, rtol=RTOL, atol=ATOL)
+            if wd:  # SB3: the returned row is the reset observation, the last one travels in infos
+                n_done += 1
+                np.testing.assert_allclose(infos[i]["terminal_observation"], wo, rtol=RTOL, atol=ATOL)
+                assert infos[i]["done_reason"] == wi["done_reason"]
+                assert infos[i]["TimeLimit.truncated"] is False
+                assert infos[i]["episode"]["l"] == o.episode_length
+                wo = o.reset(int(env.idx[i]))  # device RNG drew the frame: replay it in the oracle
+                assert env.ep_len[i] == 0
+            else:
+                assert "terminal_observation" not in infos[i]
+            assert env.idx[i] == o.idx_curr and env.ep_len[i] == o.episode_length
+            np.testing.assert_allclose(obs[i], wo, rtol=RTOL, atol=ATOL)
+    assert n_done >= steps * (n // 7)
+    env.close()
+
+
+def test_vecenv_pinned_inputs_are_zero_copy_and_equal():
+    from deepmimic_mujoco_b200.vec_env import DPVecEnv
+    from oracle.envs import SingleClipEnv
+    n = 256
+    rng = np.random.default_rng(9)
+    o = SingleClipEnv("walk", "humanoid3d")
+    q, v = _states(o, rng, n)
+    q[::7, 2] += 0.6
+    act = rng.uniform(-2, 2, (n, 28)).astype(np.float32)
+    frames = rng.integers(0, 76, n).astype(np.int32)
+    a = DPVecEnv(n, seed=1)
+    b = DPVecEnv(n, seed=1, copy_outputs=False)
+    a.reset(frame=frames)
+    b.reset(frame=frames)
+    ra = a.step(act, force_state=(q, v))
+    qb, vb, cb, ab = b.input_buffers()
+    qb[...] = q
+    vb[...] = v
+    cb[...] = 0
+    ab[...] = act
+    rb = b.step(ab, force_state=(qb, vb, cb))
+    assert rb[0] is b.obs  # the pinned output array itself
+    for x, y in zip(ra[:3], rb[:3]):
+        np.testing.assert_array_equal(x, y)
+    assert a.h2d_bytes == b.h2d_bytes and a.h2d_bytes >= n * 4 * (35 + 34 + 28)
+    a.close()
+    b.close()
+
+
+def test_lazy_infos_behaves_like_a_list_of_dicts():
+    from deepmimic_mujoco_b200.vec_env import LazyInfos
+    x = LazyInfos(5)
+    assert len(x) == 5 and x[3] == {} and x[-1] == {}
+    x[2]["k"] = 1
+    assert [d for d in x] == [{}, {}, {"k": 1}, {}, {}]
+    assert x[1:3] == [{}, {"k": 1}]
+    assert x == [{}, {}, {"k": 1}, {}, {}]
+    for i, d in enumerate(x):
+        d["i"] = i
+    assert x[4]["i"] == 4
+
+
+def test_dpenv_single_env_mirror():
+    from deepmimic_mujoco_b200 import DPEnv
+    from oracle.envs import SingleClipEnv
+    rng = np.random.default_rng(2)
+    env = DPEnv(motion="spinkick", robot="humanoid3d")
+    o = SingleClipEnv("spinkick", "humanoid3d")
+    assert env.mocap_data_len == o.mocap_data_len == 78
+    np.testing.assert_allclose(env.reset_model(idx_init=5), o.reset(5), rtol=RTOL, atol=ATOL)
+    for t in range(6):
+        q, v = _states(o, rng, 1, sig=0.3)
+        q[0, 2] += 0.6
+        act = rng.uniform(-2, 2, 28)
+        got = env.step(act, force_state=(q[0], v[0]))
+        want = o.step(act.astype(np.float32).astype(np.float64), (q[0].astype(np.float64), v[0].astype(np.float64)))
+        np.testing.assert_allclose(got[0], want[0], rtol=RTOL, atol=ATOL)
+        np.testing.assert_allclose(got[1], want[1], rtol=RTOL, atol=ATOL)
+        assert got[2] == want[2] and env.idx_curr == o.idx_curr and env.episode_length == o.episode_length
+        for k in ("reward_config", "reward_qvel", "reward_end_eff", "reward_joint_limit"):
+            if k in want[3]:
+                np.testing.assert_allclose(got[3][k], want[3][k], rtol=RTOL, atol=ATOL)
+    with pytest.raises(AssertionError):
+        env.step(np.zeros(5), force_state=(q[0], v[0]))
+    env.close()
+
+
+def test_combined_env_single_env_mirror():
+    from deepmimic_mujoco_b200 import DPCombinedEnv
+    from oracle.envs import MultiClipEnv
+    rng = np.random.default_rng(4)
+    env, o = DPCombinedEnv(), MultiClipEnv()
+    np.testing.assert_allclose(env.reset(coin=0, frame=7), o.reset(coin=0, frame=7), rtol=RTOL, atol=ATOL)
+    assert env.current_motion == "walk" and env.current_motion_n_steps == o.current_motion_n_steps
+    for t in range(5):
+        q0, v0 = o.get_current_motion_state()
+        q = (q0 + rng.normal(0, 0.01, q0.shape)).astype(np.float32)
+        v = (v0 + rng.normal(0, 0.1, v0.shape)).astype(np.float32)
+        act = rng.uniform(-0.5, 0.5, 23)
+        contact = int(rng.integers(0, 1024)) << 2
+        got = env.step(act, force_state=(q, v, contact))
+        want = o.step(act.astype(np.float32).astype(np.float64), (q.astype(np.float64), v.astype(np.float64)), contact)
+        np.testing.assert_allclose(got[0], want[0], rtol=RTOL, atol=ATOL)
+        np.testing.assert_allclose(got[1], want[1], rtol=RTOL, atol=ATOL)
+        assert got[2] == want[2] and env.current_motion_n_steps == o.current_motion_n_steps
+    env.close()
