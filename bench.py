@@ -47,6 +47,9 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--sweep-envs", default="65536,1048576")
+    ap.add_argument("--states", default="synthetic", choices=["synthetic", "recorded"],
+                    help="recorded: tile an episode_debug_log JSON (reference src/deepmimic_env.py:458-476) over the envs")
+    ap.add_argument("--recording", default=None, help="path of the episode_debug_log (default: tests/golden/recorded_<robot>_<motion>.json)")
     return ap.parse_args()
 
 
@@ -142,6 +145,23 @@ def synth_states(hp, n_envs, n_batches, seed, device, clip_ids=None):
                 ep_len=ep_len, clip=clip.contiguous())
 
 
+def recorded_states(hp, n_envs, n_batches, path, device):
+    """Env e of batch b replays step (e + b) mod T of the recorded episode (qpos / qvel / action as logged, frame index
+    idx_init + t as src/check_debug_log.py replays it)."""
+    import torch
+    from deepmimic_mujoco_b200.debug_log import read_debug_log
+    log = read_debug_log(path)
+    a = log.arrays()
+    T = len(log)
+    t = (torch.arange(n_envs, device=device)[None, :] + torch.arange(n_batches, device=device)[:, None]) % T
+    dev = lambda x, dt: torch.tensor(x, dtype=dt, device=device)
+    frames = dev(log.frame_indices(hp.clip_lens[0]), torch.int32)
+    return dict(qpos=dev(a["qpos"], torch.float32)[t].contiguous(), qvel=dev(a["qvel"], torch.float32)[t].contiguous(),
+                action=dev(a["action"], torch.float32)[t].contiguous(), contact=torch.zeros(n_batches, n_envs, dtype=torch.int32, device=device),
+                idx=frames[t].contiguous(), ep_len=t.to(torch.int32).contiguous(),
+                clip=torch.zeros(n_batches, n_envs, dtype=torch.int32, device=device))
+
+
 class Workload:
     """Resident buffers + one-step launcher for the GPU arm."""
 
@@ -160,7 +180,11 @@ class Workload:
         self.bpe = BYTES_PER_ENV_STEP[(self.hp.robot, self.kind)]
         per_batch = n_envs * self.bpe
         self.B = max(2, min(int(np.ceil(1.3 * L2_BYTES / per_batch)), 256))
-        s = synth_states(self.hp, n_envs, self.B, seed, device)
+        if args.states == "recorded":
+            path = args.recording or os.path.join(REPO, "tests", "golden", "recorded_%s_%s.json" % (self.hp.robot, args.motion.split(",")[0]))
+            s = recorded_states(self.hp, n_envs, self.B, path, device)
+        else:
+            s = synth_states(self.hp, n_envs, self.B, seed, device)
         self.soa = args.layout == "soa"
         if self.soa:
             for k in ("qpos", "qvel", "action"):
@@ -376,13 +400,32 @@ def reference_arm(args, rank):
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    RESULT.append(line)
 
 
 def workload_name(args):
     if args.combined:
         return "unitree_g1 DPCombinedEnv (walk/run/getup_facedown_towalk), %d envs per GPU" % args.envs
     return "%s DPEnv '%s', %d envs per GPU (BASELINE.json configs[1])" % (args.robot, args.motion, args.envs)
+
+
+class QuietStdout:
+    """Everything but the final JSON line goes to stderr (NCCL prints its version banner on stdout)."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+        return self
+
+    def __exit__(self, *exc):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+
+
+def emit(line):
+    print(json.dumps(line), flush=True)
 
 
 def main():
@@ -419,7 +462,8 @@ def main():
 
     line = {"metric": "env-steps/s (ref-lookup+FK+reward+obs+PD)", "value": value, "unit": "env-steps/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic" if args.states == "synthetic" else "recorded (synthetic-recorded episode_debug_log, tools/make_recording.py)",
             "config": {"workload": workload_name(args), "layout": args.layout, "state_batches": wl.B,
                        "l2_policy": "inputs larger than L2: %d distinct resident batches (%.0f MB) cycled" %
                                     (wl.B, wl.B * bytes_per_launch / 1e6),
@@ -451,12 +495,17 @@ def main():
             line["e2e"] = e2e_region(args, min(args.steps, 200), 5, 7)
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline(args, args.cpu_seconds)
-        print(json.dumps(line))
+        RESULT.append(line)
     if world > 1:
         import torch.distributed as dist
         dist.barrier()
         dist.destroy_process_group()
 
 
+RESULT = []
+
 if __name__ == "__main__":
-    main()
+    with QuietStdout():
+        main()
+    for line in RESULT:
+        emit(line)
