@@ -92,6 +92,38 @@ DM_HD float dm_rsqrt(float x) {
 }
 DM_HD double dm_rsqrt(double x) { return 1.0 / sqrt(x); }
 
+DM_HD float dm_rcp(float x) {
+#if defined(__CUDA_ARCH__)
+  return __frcp_rn(x);
+#else
+  return 1.0f / x;
+#endif
+}
+
+// atan2f, branch-free and short: a = min(|x|,|y|) / max(|x|,|y|) in [0, 1], odd minimax polynomial
+// a + a s q(s), s = a^2 (fit error 8e-9, fp32 evaluation ~1e-7 abs), octant fix-ups by selects, sign by XOR.
+// atan2(+-0, +-0) = +-0 / +-pi like libm; NaN in -> NaN out.  CUDA's atan2f is ~40 instructions with a slow-path
+// branch; the step calls it five times.
+DM_HD float dm_atan2_f(float y, float x) {
+  const float ax = fabsf(x), ay = fabsf(y);
+  const float mx = ax > ay ? ax : ay, mn = ax > ay ? ay : ax;
+  float a = mn * dm_rcp(mx);
+  a = mx == 0.0f ? 0.0f : a;                       // atan2(0, 0)
+  a = (ax == ay && ax > 3.0e38f) ? 1.0f : a;       // both infinite
+  const float s2 = a * a;
+  float q = fmaf(s2, 2.658708952e-03f, -1.528460532e-02f);
+  q = fmaf(q, s2, 4.138148949e-02f);
+  q = fmaf(q, s2, -7.390017062e-02f);
+  q = fmaf(q, s2, 1.058567539e-01f);
+  q = fmaf(q, s2, -1.418923885e-01f);
+  q = fmaf(q, s2, 1.999084800e-01f);
+  q = fmaf(q, s2, -3.333300948e-01f);
+  float r = fmaf(a * s2, q, a);
+  r = ay > ax ? 1.57079637f - r : r;
+  r = (dm_f2u(x) & 0x80000000u) ? 3.14159274f - r : r;
+  return dm_u2f(dm_f2u(r) | (dm_f2u(y) & 0x80000000u));  // r >= 0; a NaN input has already made r NaN
+}
+
 // mju_normalize4: zero quaternion -> identity
 template <typename T>
 DM_HD void dm_normalize4(T& w, T& x, T& y, T& z) {
@@ -161,6 +193,15 @@ DM_HD void dm_roll_pitch(T w, T x, T y, T z, T& roll, T& pitch) {
   pitch = asin(sp);
 }
 
+// float overload of dm_rpy (per-step path): the short atan2, asin(x) = atan2(x, sqrt(1 - x^2))
+DM_HD void dm_rpy(float w, float x, float y, float z, float& roll, float& pitch, float& yaw) {
+  roll = dm_atan2_f(2.0f * (w * x + y * z), 1.0f - 2.0f * (x * x + y * y));
+  float sp = 2.0f * (w * y - z * x);
+  sp = sp > 1.0f ? 1.0f : (sp < -1.0f ? -1.0f : sp);
+  pitch = dm_atan2_f(sp, sqrtf(fmaf(-sp, sp, 1.0f)));
+  yaw = dm_atan2_f(2.0f * (w * z + x * y), 1.0f - 2.0f * (y * y + z * z));
+}
+
 // Roll / pitch / yaw of the RAW (fp32, not necessarily unit) free-joint quaternion.  Products of fp32
 // values are exact in double, so the atan2 arguments carry no cancellation error; that keeps roll and
 // yaw accurate next to gimbal lock (the face-down get-up poses sit at pitch ~ 90 deg), where the fp32
@@ -173,9 +214,9 @@ DM_HD void dm_rpy_raw(float wf, float xf, float yf, float zf, float& roll, float
   const double yn = 2.0 * (w * z + x * y), yd = n2 - 2.0 * (yy + zz);
   const double sp = 2.0 * (w * y - z * x);
   const double cp2 = yn * yn + yd * yd;  // = (n2 cos(pitch))^2
-  roll = atan2f((float)rn, (float)rd);
-  yaw = atan2f((float)yn, (float)yd);
-  pitch = atan2f((float)sp, sqrtf((float)cp2));
+  roll = dm_atan2_f((float)rn, (float)rd);
+  yaw = dm_atan2_f((float)yn, (float)yd);
+  pitch = dm_atan2_f((float)sp, sqrtf((float)cp2));
   if (!(n2 >= 1e-30)) {  // mju_normalize4 turns a zero quaternion into identity
     if (n2 == n2) { roll = 0.0f; pitch = 0.0f; yaw = 0.0f; }
   }

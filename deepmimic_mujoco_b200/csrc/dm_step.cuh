@@ -154,8 +154,7 @@ DM_HD void write_torque(IO& io) {
     if (k < Rb::NA) {
       float c = io.act(k) * Rb::kActScale;
       // mju_clip(ctrl, lo, hi) = max(lo, min(hi, ctrl)); NaN passes through
-      c = c > Rb::ctrl_hi(k) ? Rb::ctrl_hi(k) : c;
-      c = c < Rb::ctrl_lo(k) ? Rb::ctrl_lo(k) : c;
+      c = dm_max_nan(dm_min_nan(c, Rb::ctrl_hi(k)), Rb::ctrl_lo(k));
       t = Rb::gear(k) * c;
     }
     io.tau(k, t);
@@ -168,8 +167,29 @@ struct RewardMid {
   float vx_ref, vy_ref;  // v*_xy of the frame (task reward of the combined env)
 };
 
+// FK sink of the per-step path: the squared end-effector error (deepmimic_env.py:229-233) is accumulated the
+// moment each end-effector position exists, instead of keeping 12 coordinates live until the reward (at 128
+// registers per thread those were exactly the values ptxas spilled).
+template <class Rb>
+struct EeSink {
+  static constexpr bool kWantsGeoms = false;
+  const float* __restrict__ tgt;  // the frame's 4 x 3 target positions (RowLayout::EE)
+  float e2;
+  template <typename T> DM_HD void body(int, T, T, T) {}
+  DM_HD void geom(int g, float x, float y, float z) {  // g is a literal in the generated code
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (g == Rb::ee_geom(k)) {
+        const float dx = x - tgt[3 * k], dy = y - tgt[3 * k + 1], dz = z - tgt[3 * k + 2];
+        e2 = fmaf(dx, dx, e2);
+        e2 = fmaf(dy, dy, e2);
+        e2 = fmaf(dz, dz, e2);
+      }
+  }
+};
+
 template <class Rb, class IO, bool WANT_COM>
-DM_HD float imitation_reward(const IO& io, const FkOut<float>& fk, const float* root_rpy,
+DM_HD float imitation_reward(const IO& io, const FkOut<float>& fk, const float* root_rpy, float e_ee,
                              const float* __restrict__ row, StepOut& so, RewardMid& mid) {
   using RL = RowLayout<Rb>;
   float e_q = 0.0f, e_v = 0.0f, mx = 0.0f;
@@ -203,12 +223,6 @@ DM_HD float imitation_reward(const IO& io, const FkOut<float>& fk, const float* 
   mid.d_pitch = fabsf(pitch - T(1));
   const float r_pose = expf(-(e_q + mid.d_pitch));
   const float r_vel = expf(-0.1f * e_v);
-  float e_ee = 0.0f;
-#pragma unroll
-  for (int k = 0; k < 12; ++k) {
-    const float d = fk.ee[k] - T(2 + k);
-    e_ee = fmaf(d, d, e_ee);
-  }
   const float r_ee = expf(-40.0f * e_ee);
   float r_com = 0.0f;
   if (WANT_COM) {
@@ -246,7 +260,7 @@ DM_HD void env_step(IO& io, const ClipSet& cs, const float* __restrict__ rows, E
   write_torque<Rb>(io);
 
   FkOut<float> fk;
-  NullSink sink;
+  EeSink<Rb> sink{row + RL::EE, 0.0f};
   Rb::template fk<float>(io, fk, sink);
 
   float root_rpy[3];
@@ -255,7 +269,7 @@ DM_HD void env_step(IO& io, const ClipSet& cs, const float* __restrict__ rows, E
   write_obs<KIND, Rb>(io, fk, root_rpy, contact, frame, cd.len, clip0, omax, omin);
 
   RewardMid mid;
-  const float imit = imitation_reward<Rb, IO, WANT_TERMS>(io, fk, root_rpy, row, so, mid);
+  const float imit = imitation_reward<Rb, IO, WANT_TERMS>(io, fk, root_rpy, sink.e2, row, so, mid);
   const float z = fk.com[2];
   so.terms[7] = z;
   bool done = false;

@@ -74,22 +74,36 @@ __device__ __forceinline__ void l2_prefetch(const void* src, uint32_t bytes) {
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
 }
 
+// streaming global loads that bypass L1 allocation: the tile kernel leaves the SM only ~30-60 KB of L1, which the
+// register spills (local memory) need more than one-touch inputs do
+__device__ __forceinline__ float4 ld_stream4(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+template <class T>
+__device__ __forceinline__ T ld_stream(const T* p) {
+  static_assert(sizeof(T) == 4, "32-bit");
+  uint32_t v;
+  asm volatile("ld.global.nc.L1::no_allocate.b32 %0, [%1];" : "=r"(v) : "l"(p));
+  return *reinterpret_cast<T*>(&v);
+}
+
 template <int KIND, class Rb>
 struct TileCfg {
   using OL = ObsLayout<KIND, Rb>;
   static constexpr int TE = 128;                       // environments per tile = threads per group
   static constexpr int NCOMP = OL::DIM - 2 * Rb::NJ;  // computed obs entries (torso, contacts, phase, player action)
-  static constexpr int ROW = (Rb::NQ + Rb::NV) > OL::DIM ? (Rb::NQ + Rb::NV) : OL::DIM;
-  static constexpr int NXC = 5;                        // extra statistics columns: 1, reward, done, ep_return, ep_len
-  static constexpr int NCOLS = OL::DIM + NXC, NCOLIT = (NCOLS + 31) / 32;
-  // per group: the tile buffer (input rows, later the observation tile), the extra columns, the running sums
-  static constexpr int BUF_FLOATS = TE * ROW, XC_FLOATS = TE * NXC;
-  static constexpr size_t GROUP_BYTES = sizeof(float) * (BUF_FLOATS + XC_FLOATS);
-  static constexpr size_t ACC_BYTES = sizeof(double) * 2 * NCOLIT * TE;  // per group, STATS only
+  // a tile buffer row: the input rows (nq + nv floats), later the observation row plus one statistics column (reward)
+  static constexpr int ROW = (Rb::NQ + Rb::NV) > OL::DIM + 1 ? (Rb::NQ + Rb::NV) : OL::DIM + 1;
+  static constexpr int NCOLS = OL::DIM + 1, NCOLIT = (NCOLS + 31) / 32;
+  static constexpr int BUF_FLOATS = TE * ROW;
+  static constexpr size_t BUF_BYTES = sizeof(float) * BUF_FLOATS;              // one ring slot
+  static constexpr size_t ACC_BYTES = sizeof(double) * (2 * NCOLIT * TE + 4);  // per group, STATS only
+  static constexpr int MAXBUF = 6;                                             // ring slots (mbarriers 0 .. MAXBUF-1, table = MAXBUF)
   static constexpr int NUP = (Rb::NU + 3) / 4 * 4;
-  static constexpr int MAXG = 4;
   static constexpr size_t FIXED_BYTES = 128 + sizeof(float) * 3 * NUP;  // mbarriers + motor table (gear | lo | hi)
-  static_assert(FIXED_BYTES % 16 == 0 && GROUP_BYTES % 16 == 0, "alignment");
+  static_assert(FIXED_BYTES % 16 == 0 && BUF_BYTES % 128 == 0, "alignment");
   static constexpr size_t SMEM_BUDGET = 227 * 1024;
 };
 
@@ -117,14 +131,15 @@ struct KernelGroups {  // measured on humanoid3d: G = 5 (96 registers, ~330 B of
 };
 template <>
 struct KernelGroups<Robot_unitree_g1> {  // 37 hinges: the joint blocks alone are 74 live registers when the tile is written
-  static constexpr int G = 3;
+  static constexpr int G = 3;  // measured at 1 M envs: G = 3 (168 regs) 407 us, G = 2 (254 regs, no spills) 484 us, G = 4 (128 regs) 462 us
 };
 
 struct TileExtra {
   double* acc;       // statistics accumulators or NULL
   int n_tiles;       // full tiles in this launch
   int table_floats;  // packed clip table size (floats); staged in shared memory when TABLE_SMEM
-  int l2_prefetch;   // != 0: pull the group's next tile into L2 behind the current one
+  int nbuf;          // ring slots (>= groups per CTA); nbuf - groups tiles are always loading ahead of the groups
+  int skip_compute;  // experiment: memory skeleton only (no env_step)
 };
 
 __device__ __forceinline__ void group_sync(int group) {  // named barrier 1 + group, 128 threads
@@ -135,35 +150,49 @@ template <int KIND, class Rb, bool TERMS, bool STATS, bool TABLE_SMEM, int G>
 __global__ void __launch_bounds__(128 * G, 1) step_tile_kernel(const __grid_constant__ StepParams p, const TileExtra x) {
   using OL = ObsLayout<KIND, Rb>;
   using TC = TileCfg<KIND, Rb>;
-  constexpr int TE = TC::TE, NJ = Rb::NJ, DIM = OL::DIM, NCOMP = TC::NCOMP, NCOLIT = TC::NCOLIT, NXC = TC::NXC;
+  constexpr int TE = TC::TE, NJ = Rb::NJ, DIM = OL::DIM, NCOMP = TC::NCOMP, NCOLIT = TC::NCOLIT;
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);      // [0..MAXG) group barriers, [MAXG] table barrier
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);      // [0..MAXBUF) ring-slot barriers, [MAXBUF] table barrier
   float* s_motor = reinterpret_cast<float*>(smem_raw + 128);   // [3][NUP]
   float* s_table = reinterpret_cast<float*>(smem_raw + TC::FIXED_BYTES);
-  const int n_groups = blockDim.x / TE;
+  const int n_groups = blockDim.x / TE, nbuf = x.nbuf;
   const int tid = threadIdx.x, group = tid / TE, gt = tid % TE, lane = tid & 31, warp = gt >> 5;
-  float* s_groups = s_table + (TABLE_SMEM ? x.table_floats : 0);
-  float* buf = s_groups + (size_t)group * (TC::BUF_FLOATS + TC::XC_FLOATS);
-  float* s_qp = buf;
-  float* s_qv = buf + TE * Rb::NQ;
-  float* s_xc = buf + TC::BUF_FLOATS;  // [TE][NXC]
-  // running column sums of this thread: my_acc[k * TE], k < NCOLIT sums, then NCOLIT sums of squares
-  double* my_acc = reinterpret_cast<double*>(s_groups + (size_t)n_groups * (TC::BUF_FLOATS + TC::XC_FLOATS)) +
-                   (size_t)group * 2 * NCOLIT * TE + gt;
-  uint64_t* bar = bars + group;
+  float* s_ring = s_table + (TABLE_SMEM ? x.table_floats : 0);  // nbuf slots of BUF_FLOATS
+  // running sums of this group: [2 NCOLIT][TE] per-thread column sums / sums of squares, then n_done, sum ep_return,
+  // sum ep_len of finished episodes, tiles processed
+  double* g_acc = reinterpret_cast<double*>(s_ring + (size_t)nbuf * TC::BUF_FLOATS) + (size_t)group * (2 * NCOLIT * TE + 4);
+  double* my_acc = g_acc + gt;
+  double* g_done = g_acc + 2 * NCOLIT * TE;
+  // this CTA's tiles are blockIdx.x + j * gridDim.x, j = 0 .. nt-1; tile j sits in ring slot j % nbuf and is
+  // processed by group j % n_groups
+  const int nt = (int)blockIdx.x < x.n_tiles ? (x.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  auto issue_load = [&](int j) {  // one thread
+    const int slot = j % nbuf;
+    const long long f0 = ((long long)blockIdx.x + (long long)j * gridDim.x) * TE;
+    float* dst = s_ring + (size_t)slot * TC::BUF_FLOATS;
+    mbar_expect_tx(bars + slot, sizeof(float) * TE * (Rb::NQ + Rb::NV));
+    tma_load_1d(dst, p.qpos + f0 * Rb::NQ, sizeof(float) * TE * Rb::NQ, bars + slot);
+    tma_load_1d(dst + TE * Rb::NQ, p.qvel + f0 * Rb::NV, sizeof(float) * TE * Rb::NV, bars + slot);
+  };
 
   if (tid == 0) {
-    for (int g = 0; g <= TC::MAXG; ++g) mbar_init(bars + g, 1);
+    for (int g = 0; g <= TC::MAXBUF; ++g) mbar_init(bars + g, 1);
     mbar_fence_init();
   }
   if (STATS) {
 #pragma unroll
     for (int k = 0; k < 2 * NCOLIT; ++k) my_acc[k * TE] = 0.0;
+    if (gt < 4) g_done[gt] = 0.0;
   }
   __syncthreads();
+  if (gt == 0) {  // fill the ring: every leader its own first tile, leader 0 the slots beyond the groups
+    if (group < nt) issue_load(group);
+    if (group == 0)
+      for (int j = n_groups; j < nbuf && j < nt; ++j) issue_load(j);
+  }
   if (TABLE_SMEM && tid == 0) {
-    mbar_expect_tx(bars + TC::MAXG, sizeof(float) * x.table_floats);
-    tma_load_1d(s_table, p.cs.rows, sizeof(float) * x.table_floats, bars + TC::MAXG);
+    mbar_expect_tx(bars + TC::MAXBUF, sizeof(float) * x.table_floats);
+    tma_load_1d(s_table, p.cs.rows, sizeof(float) * x.table_floats, bars + TC::MAXBUF);
   }
   const float* rows = TABLE_SMEM ? s_table : p.cs.rows;
 
@@ -179,12 +208,11 @@ __global__ void __launch_bounds__(128 * G, 1) step_tile_kernel(const __grid_cons
   }
   __syncthreads();
 
-  uint32_t parity = 0;
   bool table_ready = !TABLE_SMEM;
-  const int tstride = gridDim.x * n_groups;
   // Software pipeline through registers: the per-env scalars and (128-bit path) the action chunks of a tile are
   // loaded one tile AHEAD, right after the previous tile's observation store is issued, so their global-load
   // latency hides behind the statistics pass and the barrier instead of stalling every warp of the group.
+  // (Running the whole torque pass of the next tile there instead was measured slower: 188 vs 179 us at 1 M envs.)
   constexpr bool kVecTorque = Rb::NA == Rb::NU && Rb::NA % 4 == 0;
   constexpr int K4 = Rb::NA / 4, CH = TE * Rb::NA / 4, PER = kVecTorque ? (CH + TE - 1) / TE : 1;
   float4 av[PER];
@@ -194,44 +222,26 @@ __global__ void __launch_bounds__(128 * G, 1) step_tile_kernel(const __grid_cons
   auto load_ahead = [&](int t) {
     const long long f0 = (long long)t * TE;
     const int e = int(f0) + gt;
-    st_n.idx = p.idx[e];
-    st_n.ep_len = p.ep_len[e];
-    st_n.clip = p.clip ? p.clip[e] : 0;
-    contact_n = p.contact ? p.contact[e] : 0u;
-    ep_ret_n = p.ep_return ? p.ep_return[e] : 0.0f;
+    st_n.idx = ld_stream(p.idx + e);
+    st_n.ep_len = ld_stream(p.ep_len + e);
+    st_n.clip = p.clip ? ld_stream(p.clip + e) : 0;
+    contact_n = p.contact ? ld_stream(p.contact + e) : 0u;
+    ep_ret_n = p.ep_return ? ld_stream(p.ep_return + e) : 0.0f;
     if (kVecTorque && p.torque) {
       const float4* a4 = reinterpret_cast<const float4*>(p.action + f0 * Rb::NA);
 #pragma unroll
       for (int m = 0; m < PER; ++m)
-        if (gt + m * TE < CH) av[m] = __ldg(a4 + gt + m * TE);
+        if (gt + m * TE < CH) av[m] = ld_stream4(a4 + gt + m * TE);
     }
   };
-  int tile = blockIdx.x * n_groups + group;
-  if (tile < x.n_tiles) load_ahead(tile);
-  for (; tile < x.n_tiles; tile += tstride) {
-    const long long e0 = (long long)tile * TE;
-    if (gt == 0) {
-      bulk_wait_read0();  // the previous tile's observation store is done reading this buffer
-      mbar_expect_tx(bar, sizeof(float) * TE * (Rb::NQ + Rb::NV));
-      tma_load_1d(s_qp, p.qpos + e0 * Rb::NQ, sizeof(float) * TE * Rb::NQ, bar);
-      tma_load_1d(s_qv, p.qvel + e0 * Rb::NV, sizeof(float) * TE * Rb::NV, bar);
-      const int nxt = tile + tstride;  // pull the group's next tile into L2 behind this one
-      if (x.l2_prefetch && nxt < x.n_tiles) {
-        const long long n0 = (long long)nxt * TE;
-        l2_prefetch(p.qpos + n0 * Rb::NQ, sizeof(float) * TE * Rb::NQ);
-        l2_prefetch(p.qvel + n0 * Rb::NV, sizeof(float) * TE * Rb::NV);
-      }
-    }
-    const int env = int(e0) + gt;
-    EnvState st = st_n;
-    const uint32_t contact = contact_n;
-    const float ep_ret0 = ep_ret_n;
-    // ---- action -> torque: a flat, fully coalesced pass over the [TE, NA] tile (contiguous in the row-major
-    //      action array) ----------------------------------------------------------------------------------------
+  // action -> torque of tile t: a flat, fully coalesced pass over the [TE, NA] tile (contiguous in the row-major
+  // action array)
+  auto torque_tile = [&](int t) {
+    const long long e0 = (long long)t * TE;
     if (p.torque) {
-      if (kVecTorque) {  // 128-bit path: chunk c covers actuators 4 (c mod NA/4) .. + 3; loaded a tile ahead
+      if (kVecTorque) {  // 128-bit path: chunk c covers actuators 4 (c mod NA/4) .. + 3; av[] was loaded by load_ahead
         float4* t4 = reinterpret_cast<float4*>(p.torque + e0 * Rb::NU);
-        const int r4 = gt % K4;  // (gt + m TE) mod K4 from one remainder: nothing per-m to keep live (or spill)
+        const int r4 = gt % K4;
 #pragma unroll
         for (int m = 0; m < PER; ++m) {
           const int c = gt + m * TE;
@@ -244,10 +254,11 @@ __global__ void __launch_bounds__(128 * G, 1) step_tile_kernel(const __grid_cons
             const float4 hi = *reinterpret_cast<const float4*>(s_motor + 2 * TC::NUP + k0);
             float4 o;
             float c0 = av[m].x * Rb::kActScale, c1 = av[m].y * Rb::kActScale, c2 = av[m].z * Rb::kActScale, c3 = av[m].w * Rb::kActScale;
-            c0 = c0 > hi.x ? hi.x : c0; c0 = c0 < lo.x ? lo.x : c0; o.x = g.x * c0;
-            c1 = c1 > hi.y ? hi.y : c1; c1 = c1 < lo.y ? lo.y : c1; o.y = g.y * c1;
-            c2 = c2 > hi.z ? hi.z : c2; c2 = c2 < lo.z ? lo.z : c2; o.z = g.z * c2;
-            c3 = c3 > hi.w ? hi.w : c3; c3 = c3 < lo.w ? lo.w : c3; o.w = g.w * c3;
+            // mju_clip with NaN passing through: min.NaN / max.NaN, one instruction each
+            o.x = g.x * dm_max_nan(dm_min_nan(c0, hi.x), lo.x);
+            o.y = g.y * dm_max_nan(dm_min_nan(c1, hi.y), lo.y);
+            o.z = g.z * dm_max_nan(dm_min_nan(c2, hi.z), lo.z);
+            o.w = g.w * dm_max_nan(dm_min_nan(c3, hi.w), lo.w);
             t4[c] = o;
           }
         }
@@ -269,36 +280,54 @@ __global__ void __launch_bounds__(128 * G, 1) step_tile_kernel(const __grid_cons
             if (h * HALF + m < PERS && o < TOT) {
               float c = v[m] * Rb::kActScale;
               const float hi = s_motor[2 * TC::NUP + k], lo = s_motor[TC::NUP + k];
-              c = c > hi ? hi : c;
-              c = c < lo ? lo : c;
+              c = dm_max_nan(dm_min_nan(c, hi), lo);
               trow[o] = k < Rb::NA ? s_motor[k] * c : 0.0f;
             }
           }
         }
       }
     }
+  };
+  auto tile_of = [&](int j) { return (int)blockIdx.x + j * (int)gridDim.x; };
+  if (group < nt) load_ahead(tile_of(group));
+  int done_tiles = 0;
+  for (int j = group; j < nt; j += n_groups, ++done_tiles) {
+    const int slot = j % nbuf;
+    const uint32_t parity = (j / nbuf) & 1;
+    float* buf = s_ring + (size_t)slot * TC::BUF_FLOATS;
+    const float* s_qp = buf;
+    const float* s_qv = buf + TE * Rb::NQ;
+    float* s_rw = buf + TE * DIM;  // the reward column of the finished tile (statistics), behind the observation rows
+    const long long e0 = (long long)tile_of(j) * TE;
+    const int env = int(e0) + gt;
+    EnvState st = st_n;
+    const uint32_t contact = contact_n;
+    const float ep_ret0 = ep_ret_n;
+    torque_tile(tile_of(j));  // while the TMA load is in flight; its action chunks were loaded a tile ahead
     // ---- per-environment step out of shared memory --------------------------------------------------
     if (!table_ready) {
-      mbar_wait(bars + TC::MAXG, 0);
+      mbar_wait(bars + TC::MAXBUF, 0);
       table_ready = true;
     }
-    mbar_wait(bar, parity);
-    parity ^= 1u;
+    mbar_wait(bars + slot, parity);
     TileIO<KIND, Rb> io;
     io.qp = s_qp + gt * Rb::NQ;
     io.qv = s_qv + gt * Rb::NV;
     StepOut so;
-    env_step<KIND, Rb, TileIO<KIND, Rb>, TERMS>(io, p.cs, rows, st, contact, so);
+    if (!x.skip_compute) {
+      env_step<KIND, Rb, TileIO<KIND, Rb>, TERMS>(io, p.cs, rows, st, contact, so);
+    } else {
+      so.reward = so.raw_reward = io.qp[2]; so.done = 0; so.reason = 0;
+#pragma unroll
+      for (int j = 0; j < NCOMP; ++j) io.co[j] = io.qv[j];
+    }
     finish_env<KIND, Rb, TERMS, false>(p, env, st, so);
     const float ep_ret1 = ep_ret0 + so.raw_reward;
     if (p.ep_return) p.ep_return[env] = ep_ret1;
-    if (STATS) {
-      float* xc = s_xc + gt * NXC;
-      xc[0] = 1.0f;
-      xc[1] = so.reward;
-      xc[2] = so.done ? 1.0f : 0.0f;
-      xc[3] = so.done ? ep_ret1 : 0.0f;
-      xc[4] = so.done ? float(st.ep_len) : 0.0f;
+    if (STATS && so.done) {  // finished episodes are rare: shared-memory fp64 atomics
+      atomicAdd(g_done + 0, 1.0);
+      atomicAdd(g_done + 1, double(ep_ret1));
+      atomicAdd(g_done + 2, double(st.ep_len));
     }
     const bool guard = so.reason == R_OBS_BOUNDS;
     // ---- observation tile in place: joint blocks -> registers, sync, finished rows over the input rows ----------
@@ -311,11 +340,16 @@ __global__ void __launch_bounds__(128 * G, 1) step_tile_kernel(const __grid_cons
       group_sync(group);  // every input row of the tile is dead
       float* orow = buf + gt * DIM;
 #pragma unroll
-      for (int j = 0; j < NJ; ++j) orow[j] = guard ? 0.0f : jq[j];
+      for (int j = 0; j < NJ; ++j) orow[j] = jq[j];
 #pragma unroll
-      for (int j = 0; j < NJ; ++j) orow[NJ + j] = guard ? 0.0f : jv[j];
+      for (int j = 0; j < NJ; ++j) orow[NJ + j] = jv[j];
 #pragma unroll
-      for (int j = 0; j < NCOMP; ++j) orow[2 * NJ + j] = guard ? 0.0f : io.co[j];
+      for (int j = 0; j < NCOMP; ++j) orow[2 * NJ + j] = io.co[j];
+      if (STATS) s_rw[gt] = so.reward;
+      if (guard) {  // observation-bounds guard: the row leaves as zeros (rare; kept off the straight-line path)
+#pragma unroll 1
+        for (int j = 0; j < DIM; ++j) orow[j] = 0.0f;
+      }
     }
     fence_async_smem();
     group_sync(group);
@@ -323,16 +357,16 @@ __global__ void __launch_bounds__(128 * G, 1) step_tile_kernel(const __grid_cons
       tma_store_1d(p.obs + e0 * DIM, buf, sizeof(float) * TE * DIM);
       bulk_commit();
     }
-    if (tile + tstride < x.n_tiles) load_ahead(tile + tstride);
+    if (j + n_groups < nt) load_ahead(tile_of(j + n_groups));
     if (STATS) {  // column sums of the finished tile: lanes walk columns, the group's warps walk rows
       float cs32[NCOLIT], css32[NCOLIT];
 #pragma unroll
       for (int it = 0; it < NCOLIT; ++it) {
         cs32[it] = css32[it] = 0.0f;
-        const int j = it * 32 + lane;
-        if (j < DIM + NXC) {
-          const float* src = j < DIM ? buf + warp * DIM + j : s_xc + warp * NXC + (j - DIM);
-          const int stride = 4 * (j < DIM ? DIM : NXC);
+        const int c = it * 32 + lane;
+        if (c <= DIM) {  // column DIM is the reward
+          const float* src = c < DIM ? buf + warp * DIM + c : s_rw + warp;
+          const int stride = c < DIM ? 4 * DIM : 4;
 #pragma unroll 8
           for (int r = 0; r < TE / 4; ++r) {
             const float v = src[r * stride];
@@ -347,27 +381,38 @@ __global__ void __launch_bounds__(128 * G, 1) step_tile_kernel(const __grid_cons
         my_acc[(NCOLIT + it) * TE] += css32[it];
       }
     }
-    group_sync(group);  // everyone is done reading the tile before the next TMA load overwrites it
+    group_sync(group);  // everyone is done reading the tile before a TMA load overwrites the slot
+    if (gt == 0 && j + nbuf < nt) {
+      bulk_wait_read0();  // ... and so is this tile's observation store
+      issue_load(j + nbuf);
+    }
   }
   if (gt == 0) bulk_wait_read0();  // shared memory stays valid until the last store has read it
 
   if (STATS && x.acc) {
     // CTA-level reduction of the shared-memory running sums, then ONE set of fp64 atomics per CTA
+    if (gt == 0) g_done[3] = double(done_tiles);
     __syncthreads();
-    const double* acc0 = reinterpret_cast<const double*>(s_groups + (size_t)n_groups * (TC::BUF_FLOATS + TC::XC_FLOATS));
+    const double* acc0 = reinterpret_cast<const double*>(s_ring + (size_t)nbuf * TC::BUF_FLOATS);
+    constexpr int GS = 2 * NCOLIT * TE + 4;
     auto colsum = [&](int c, int sq) {  // column c = it * 32 + lane, over every group and warp
       const int it = c >> 5, ln = c & 31;
       double v = 0.0;
       for (int g = 0; g < n_groups; ++g)
-        for (int w = 0; w < 4; ++w) v += acc0[(size_t)g * 2 * NCOLIT * TE + ((sq ? NCOLIT : 0) + it) * TE + w * 32 + ln];
+        for (int w = 0; w < 4; ++w) v += acc0[(size_t)g * GS + ((sq ? NCOLIT : 0) + it) * TE + w * 32 + ln];
+      return v;
+    };
+    auto donesum = [&](int k) {
+      double v = 0.0;
+      for (int g = 0; g < n_groups; ++g) v += acc0[(size_t)g * GS + 2 * NCOLIT * TE + k];
       return v;
     };
     for (int j = tid; j < 2 * DIM + 6; j += blockDim.x) {
       double v;
-      if (j == 0) v = colsum(DIM + 0, 0);        // count
-      else if (j == 1) v = colsum(DIM + 1, 0);   // sum r
-      else if (j == 2) v = colsum(DIM + 1, 1);   // sum r^2
-      else if (j < 6) v = colsum(DIM + j - 1, 0);  // n_done, sum ep_return(done), sum ep_len(done)
+      if (j == 0) v = donesum(3) * TE;           // count
+      else if (j == 1) v = colsum(DIM, 0);       // sum r
+      else if (j == 2) v = colsum(DIM, 1);       // sum r^2
+      else if (j < 6) v = donesum(j - 3);        // n_done, sum ep_return(done), sum ep_len(done)
       else if (j < 6 + DIM) v = colsum(j - 6, 0);
       else v = colsum(j - 6 - DIM, 1);
       if (v != 0.0) atomicAdd(x.acc + j, v);

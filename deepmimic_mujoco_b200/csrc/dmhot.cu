@@ -41,7 +41,7 @@ struct dm_handle {
   // bookkeeping
   long long launches = 0;
   int variant = -1;  // -1 auto
-  int table_smem_override = -1, max_groups_override = 0, l2_prefetch = 1;  // tuning knobs (DM_TABLE_SMEM, DM_MAX_GROUPS)
+  int table_smem_override = -1, max_groups_override = 0, nbuf_override = 0, skip_compute = 0;  // tuning knobs (DM_TABLE_SMEM, DM_MAX_GROUPS)
   bool timing = false;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev;
   size_t ev_used = 0;
@@ -96,7 +96,8 @@ extern "C" int dm_create(int device, int robot, int env_kind, dm_handle** out) {
   h->robot = robot;
   h->kind = env_kind;
   if (const char* e = getenv("DM_TABLE_SMEM")) h->table_smem_override = atoi(e);
-  if (const char* e = getenv("DM_L2_PREFETCH")) h->l2_prefetch = atoi(e);
+  if (const char* e = getenv("DM_SKIP_COMPUTE")) h->skip_compute = atoi(e);
+  if (const char* e = getenv("DM_NBUF")) h->nbuf_override = atoi(e);
   if (const char* e = getenv("DM_MAX_GROUPS")) h->max_groups_override = atoi(e);
   dispatch(h, [&](auto rb, auto kind) -> int {
     using Rb = decltype(rb);
@@ -288,21 +289,35 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
       constexpr int GMAX = KernelGroups<Rb>::G;
       const int n_tiles = tiled / TC::TE;
       const size_t table_bytes = sizeof(float) * (size_t)h->total_rows * RowLayout<Rb>::STRIDE;
-      const size_t per_group = TC::GROUP_BYTES + (a->accumulate_stats ? TC::ACC_BYTES : 0);
-      const int g_plain = (int)((TC::SMEM_BUDGET - TC::FIXED_BYTES) / per_group);
-      const int g_table = TC::FIXED_BYTES + table_bytes < TC::SMEM_BUDGET
-                              ? (int)((TC::SMEM_BUDGET - TC::FIXED_BYTES - table_bytes) / per_group) : 0;
-      // the clip table goes to shared memory when that does not cost a group of occupancy
-      bool table_smem = g_table >= (g_plain < GMAX ? g_plain : GMAX);
-      if (h->table_smem_override >= 0) table_smem = h->table_smem_override != 0 && g_table >= 1;
-      int G = table_smem ? g_table : g_plain;
+      // shared memory: fixed block, (optionally) the clip table, a ring of nbuf tile buffers, per-group running sums.
+      // Groups first (occupancy), then any extra ring slots, then the clip table if it still fits.
+      const size_t acc_bytes = a->accumulate_stats ? TC::ACC_BYTES : 0;
+      const size_t avail = TC::SMEM_BUDGET - TC::FIXED_BYTES;
+      int G = (int)(avail / (TC::BUF_BYTES + acc_bytes));
       G = G > GMAX ? GMAX : G;
       if (h->max_groups_override > 0 && h->max_groups_override < G) G = h->max_groups_override;
       const int want = (n_tiles + h->num_sms - 1) / h->num_sms;  // spread small batches over all SMs first
       G = want < G ? (want < 1 ? 1 : want) : G;
       const int grid = (n_tiles + G - 1) / G < h->num_sms ? (n_tiles + G - 1) / G : h->num_sms;
-      const size_t smem = TC::FIXED_BYTES + (table_smem ? table_bytes : 0) + (size_t)G * per_group;
-      TileExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float)), h->l2_prefetch};
+      const int tiles_per_cta = (n_tiles + grid - 1) / grid;
+      // ring slots: measured at 1 M / 4 M envs, slots beyond the groups (tiles loading while every group computes)
+      // are 3-5 % SLOWER than one slot per group, so the default ring is exactly the groups; DM_NBUF overrides
+      int nbuf_want = h->nbuf_override > 0 ? h->nbuf_override : G;
+      nbuf_want = nbuf_want > TC::MAXBUF ? TC::MAXBUF : nbuf_want;
+      nbuf_want = nbuf_want > tiles_per_cta ? tiles_per_cta : nbuf_want;  // no more slots than tiles
+      nbuf_want = nbuf_want < G ? G : nbuf_want;
+      auto fit = [&](bool table) {
+        const size_t rest = avail - G * acc_bytes;
+        if (table && table_bytes > rest) return 0;
+        const int nb = (int)((rest - (table ? table_bytes : 0)) / TC::BUF_BYTES);
+        return nb > nbuf_want ? nbuf_want : nb;
+      };
+      const int nb_table = fit(true), nb_plain = fit(false);
+      bool table_smem = nb_table >= G && (nb_table >= nb_plain || nb_table >= G + 1);
+      if (h->table_smem_override >= 0) table_smem = h->table_smem_override != 0 && nb_table >= G;
+      const int nbuf = table_smem ? nb_table : nb_plain;
+      const size_t smem = TC::FIXED_BYTES + (table_smem ? table_bytes : 0) + (size_t)nbuf * TC::BUF_BYTES + G * acc_bytes;
+      TileExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float)), nbuf, h->skip_compute};
       auto launch = [&](auto kern) -> cudaError_t {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
