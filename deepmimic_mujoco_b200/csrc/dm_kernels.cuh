@@ -48,6 +48,7 @@ struct StridedIO {
   __device__ __forceinline__ float qvel(int j) const { return __ldg(qv + j * es); }
   __device__ __forceinline__ float act(int j) const { return __ldg(ac + j * es); }
   __device__ __forceinline__ void obs(int j, float v) { ob[j * es] = v; }
+  __device__ __forceinline__ void obs_times_zero(int j) { ob[j * es] = ob[j * es] * 0.0f; }
   __device__ __forceinline__ void tau(int j, float v) {
     if (ta) ta[j * es] = v;
   }

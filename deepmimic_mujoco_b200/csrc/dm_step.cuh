@@ -336,7 +336,7 @@ DM_HD void env_step(IO& io, const ClipSet& cs, const float* __restrict__ rows, E
   if (omax > 100.0f || omin < -100.0f) {
     if constexpr (io_zeroes_on_guard<IO>::value) {
 #pragma unroll 1
-      for (int j = 0; j < OL::DIM; ++j) io.obs(j, 0.0f);
+      for (int j = 0; j < OL::DIM; ++j) io.obs_times_zero(j);  // `_get_obs() * 0.`: an infinite entry becomes NaN
     }
     so.reward = 0.0f;
     so.done = 1;

@@ -346,9 +346,10 @@ __global__ void __launch_bounds__(128 * G, 1) step_tile_kernel(const __grid_cons
 #pragma unroll
       for (int j = 0; j < NCOMP; ++j) orow[2 * NJ + j] = io.co[j];
       if (STATS) s_rw[gt] = so.reward;
-      if (guard) {  // observation-bounds guard: the row leaves as zeros (rare; kept off the straight-line path)
+      if (guard) {  // observation-bounds guard: the row leaves as `obs * 0.` (zeros; NaN where an entry was infinite,
+                    // deepmimic_env.py:476); rare, kept off the straight-line path
 #pragma unroll 1
-        for (int j = 0; j < DIM; ++j) orow[j] = 0.0f;
+        for (int j = 0; j < DIM; ++j) orow[j] = orow[j] * 0.0f;
       }
     }
     fence_async_smem();

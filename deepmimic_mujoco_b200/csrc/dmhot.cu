@@ -233,6 +233,7 @@ static int check_step_args(dm_handle* h, const dm_step_args* a, const char* who)
   if (!h || !a) return fail(h, DM_E_ARG, "%s: NULL argument", who);
   if (!h->d_rows) return fail(h, DM_E_STATE, "%s: no clips uploaded (call dm_upload_clips first)", who);
   if (a->n < 0) return fail(h, DM_E_ARG, "%s: n = %d", who, a->n);
+  if (a->n == 0) return DM_OK;  // an empty batch is a no-op; its buffers may be NULL
   if (a->layout != DM_LAYOUT_AOS && a->layout != DM_LAYOUT_SOA) return fail(h, DM_E_ARG, "%s: unknown layout %d", who, a->layout);
   if (a->layout == DM_LAYOUT_SOA && a->ld < a->n) return fail(h, DM_E_ARG, "%s: SoA ld %lld < n %d", who, (long long)a->ld, a->n);
   if (!a->qpos || !a->qvel || !a->action || !a->idx || !a->ep_len || !a->obs || !a->reward || !a->done)

@@ -17,6 +17,7 @@ struct ArrayIO {
   float qvel(int j) const { return qv[j]; }
   float act(int j) const { return ac[j]; }
   void obs(int j, float v) { ob[j] = v; }
+  void obs_times_zero(int j) { ob[j] = ob[j] * 0.0f; }
   void tau(int j, float v) { if (ta) ta[j] = v; }
 };
 struct DIO {
