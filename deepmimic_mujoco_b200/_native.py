@@ -54,7 +54,7 @@ class ResetArgs(C.Structure):
 SYMBOLS = ["dm_abi_version", "dm_create", "dm_destroy", "dm_last_error", "dm_get_dims", "dm_get_model", "dm_fk_tables",
            "dm_upload_clips", "dm_get_packed_rows", "dm_step", "dm_reset", "dm_step_host", "dm_reset_host", "dm_host_buffers",
            "dm_stats_zero", "dm_stats_device_ptr", "dm_stats_read", "dm_launch_count", "dm_step_kernel_time",
-           "dm_set_timing", "dm_set_kernel_variant"]
+           "dm_set_timing", "dm_set_kernel_variant", "dm_set_contact_mode"]
 
 _lib = None
 
@@ -89,6 +89,7 @@ def lib():
     L.dm_step_kernel_time.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
     L.dm_set_timing.argtypes = [C.c_void_p, C.c_int]
     L.dm_set_kernel_variant.argtypes = [C.c_void_p, C.c_int]
+    L.dm_set_contact_mode.argtypes = [C.c_void_p, C.c_int]
     _lib = L
     return L
 

@@ -229,7 +229,8 @@ __global__ void __launch_bounds__(128) reset_kernel(const __grid_constant__ Rese
   float root_rpy[3];
   dm_rpy_raw(io.qpos(3), io.qpos(4), io.qpos(5), io.qpos(6), root_rpy[0], root_rpy[1], root_rpy[2]);
   float omax, omin;
-  write_obs<KIND, Rb>(io, fk, root_rpy, p.contact ? p.contact[env] : 0u, frame, cd.len, clip, omax, omin);
+  const uint32_t contact = p.cs.contact_from_fk ? fk.contact : (p.contact ? p.contact[env] : 0u);
+  write_obs<KIND, Rb>(io, fk, root_rpy, contact, frame, cd.len, clip, omax, omin);
 }
 
 // ---- K4: statistics ----------------------------------------------------------------------------

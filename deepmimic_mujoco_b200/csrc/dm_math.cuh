@@ -23,6 +23,7 @@ struct FkOut {
   T com_xpos[3];  // sum(m * xpos) / sum(m)    (the reward's "C.O.M", deepmimic_env.py:235-238)
   T ee[12];       // 4 end-effector geom_xpos, RobotConfig.endeffector_geom_names order
   T cvel[6];      // torso cvel: [angular; linear]
+  uint32_t contact;  // floor contacts derived from FK (bit layout of the dm_step_args contact word)
 };
 
 struct NullSink {
@@ -31,6 +32,8 @@ struct NullSink {
   template <typename T> DM_HD void geom(int, T, T, T) {}
 };
 
+DM_HD float dm_abs(float a) { return fabsf(a); }
+DM_HD double dm_abs(double a) { return fabs(a); }
 DM_HD float dm_fma(float a, float b, float c) { return fmaf(a, b, c); }
 DM_HD double dm_fma(double a, double b, double c) { return fma(a, b, c); }
 

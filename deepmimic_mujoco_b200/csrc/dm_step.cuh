@@ -49,6 +49,7 @@ constexpr int kMaxClips = 8;
 struct ClipSet {
   const float* rows;
   int n_clips;
+  int contact_from_fk;  // != 0: floor-contact bits come from FK (generated plane-sphere / plane-box tests), not the caller
   ClipDesc clip[kMaxClips];
 };
 
@@ -263,6 +264,7 @@ DM_HD void env_step(IO& io, const ClipSet& cs, const float* __restrict__ rows, E
   EeSink<Rb> sink{row + RL::EE, 0.0f};
   Rb::template fk<float>(io, fk, sink);
 
+  if (cs.contact_from_fk) contact = fk.contact;
   float root_rpy[3];
   dm_rpy_raw(io.qpos(3), io.qpos(4), io.qpos(5), io.qpos(6), root_rpy[0], root_rpy[1], root_rpy[2]);
   float omax, omin;

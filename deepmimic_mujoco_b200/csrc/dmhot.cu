@@ -41,6 +41,7 @@ struct dm_handle {
   // bookkeeping
   long long launches = 0;
   int variant = -1;  // -1 auto
+  int contact_mode = 0;  // DM_CONTACT_*
   int table_smem_override = -1, max_groups_override = 0, nbuf_override = 0, skip_compute = 0;  // tuning knobs (DM_TABLE_SMEM, DM_MAX_GROUPS)
   bool timing = false;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev;
@@ -277,6 +278,7 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
     p.obs = a->obs; p.reward = a->reward; p.done = a->done; p.reason = a->reason;
     p.torque = a->torque; p.terms = a->terms; p.ep_return = a->ep_return;
     p.cs = h->cs;
+    p.cs.contact_from_fk = h->contact_mode;
     // K1b (shared-memory tiles, TMA in / TMA out) for the full 128-env tiles of a row-major batch, K1a for the rest
     const bool aligned = ((reinterpret_cast<uintptr_t>(a->qpos) | reinterpret_cast<uintptr_t>(a->qvel) |
                            reinterpret_cast<uintptr_t>(a->obs) | reinterpret_cast<uintptr_t>(a->action) |
@@ -386,6 +388,7 @@ static int launch_reset(dm_handle* h, const dm_reset_args* a, cudaStream_t s) {
     p.seed = a->seed; p.counter = a->counter;
     p.qpos = a->qpos; p.qvel = a->qvel; p.idx = a->idx; p.ep_len = a->ep_len; p.clip = a->clip;
     p.obs = a->obs; p.ep_return = a->ep_return; p.terminal_obs = a->terminal_obs; p.state_rows = h->d_state_rows; p.cs = h->cs;
+    p.cs.contact_from_fk = h->contact_mode;
     reset_kernel<KIND, Rb><<<(a->n + 127) / 128, 128, 0, s>>>(p);
     h->launches++;
     CU(h, cudaGetLastError());
@@ -631,6 +634,11 @@ extern "C" int dm_step_kernel_time(dm_handle* h, int reset, double* avg_ms, int6
   if (avg_ms) *avg_ms = h->t_n ? h->t_ms / h->t_n : 0.0;
   if (launches) *launches = h->t_n;
   if (reset) { h->t_ms = 0; h->t_n = 0; }
+  return DM_OK;
+}
+extern "C" int dm_set_contact_mode(dm_handle* h, int mode) {
+  if (!h || (mode != DM_CONTACT_CALLER && mode != DM_CONTACT_FROM_FK)) return fail(h, DM_E_ARG, "dm_set_contact_mode: mode must be 0 or 1");
+  h->contact_mode = mode;
   return DM_OK;
 }
 extern "C" int dm_set_kernel_variant(dm_handle* h, int variant) {

@@ -257,5 +257,9 @@ class HotPath:
         N.check(self.L.dm_step_kernel_time(self.h, 1 if reset else 0, C.byref(ms), C.byref(n)), self.h, "dm_step_kernel_time")
         return ms.value, n.value
 
+    def set_contact_mode(self, from_fk):
+        """True: the floor-contact observation bits are derived from FK inside the kernels (include/dmhot.h)."""
+        N.check(self.L.dm_set_contact_mode(self.h, 1 if from_fk else 0), self.h, "dm_set_contact_mode")
+
     def set_kernel_variant(self, v):
         N.check(self.L.dm_set_kernel_variant(self.h, int(v)), self.h, "dm_set_kernel_variant")

@@ -199,6 +199,7 @@ def compile_mjcf(path, name=None) -> RobotModel:
                 "mass": float(a["mass"]) if "mass" in a else None,
                 "density": float(a.get("density", _GEOM_DENSITY)),
                 "contype": int(a.get("contype", 1)), "conaffinity": int(a.get("conaffinity", 1)),
+                "margin": float(a.get("margin", 0.0)), "has_quat": any(k in a for k in ("quat", "euler", "axisangle", "xyaxes", "zaxis")),
             })
 
     def walk(elem, pid, childclass):
@@ -307,6 +308,11 @@ def compile_mjcf(path, name=None) -> RobotModel:
         actuator_names=an, actuator_jntid=i64(ajid), actuator_dofadr=i64(adof), actuator_gear=f64(agear),
         actuator_ctrlrange=f64(arng, (-1, 2)), actuator_ctrllimited=np.asarray(alim, dtype=bool),
         timestep=timestep,
+        # collision geometry of the floor-contact observation (deepmimic_env.py:78-121): type, half sizes, margin
+        extra={"geom_type": [g["type"] for b in range(len(body_names)) for g in per_body_geoms[b]],
+               "geom_size": [(list(g["size"]) + [0.0, 0.0, 0.0])[:3] for b in range(len(body_names)) for g in per_body_geoms[b]],
+               "geom_margin": [g["margin"] for b in range(len(body_names)) for g in per_body_geoms[b]],
+               "geom_has_quat": [bool(g["has_quat"]) for b in range(len(body_names)) for g in per_body_geoms[b]]},
     )
 
 

@@ -72,7 +72,7 @@ class LazyInfos(list):
 
 class DPVecEnv:
     def __init__(self, num_envs, motion="walk", robot="humanoid3d", combined=False, device=0, seed=0, physics=None,
-                 info_terms=False, copy_outputs=True):
+                 info_terms=False, copy_outputs=True, contact_from_fk=False):
         self.num_envs = int(num_envs)
         self.robot = "unitree_g1" if combined else robot
         self.combined = bool(combined)
@@ -86,6 +86,7 @@ class DPVecEnv:
         else:
             self.motions = [motion] if isinstance(motion, str) else list(motion)
             self.hp.load_motions(self.motions)
+        self.hp.set_contact_mode(contact_from_fk)
         d = self.hp.dims
         mc = self.hp.model_constants()
         lo, hi = mc["ctrl_lo"][:d.na].copy(), mc["ctrl_hi"][:d.na].copy()

@@ -174,6 +174,14 @@ int dm_launch_count(const dm_handle* h, int64_t* kernels);
  * with reset != 0; used for the roofline line */
 int dm_step_kernel_time(dm_handle* h, int reset, double* avg_ms, int64_t* launches);
 int dm_set_timing(dm_handle* h, int enabled);
+/* Where the floor-contact bits of the observation come from (get_foot_contact_obs / get_extra_contact_obs,
+ * src/deepmimic_env.py:78-121, read mjdata.contact):
+ *   DM_CONTACT_CALLER  the `contact` words of dm_step_args / dm_reset_args (NULL = no contacts)      [default]
+ *   DM_CONTACT_FROM_FK derived inside the kernels from forward kinematics: MuJoCo's plane-sphere / plane-box test of
+ *                      the foot / heel / toe geoms against the floor plane, contact iff dist <= max(margins); the
+ *                      caller's words are ignored.  Restated from MuJoCo 2.1 (parity unpinned: no MuJoCo here). */
+enum { DM_CONTACT_CALLER = 0, DM_CONTACT_FROM_FK = 1 };
+int dm_set_contact_mode(dm_handle* h, int mode);
 /* 0 = generic strided kernel, 1 = shared-memory tile kernel with TMA bulk copies (AoS only); default auto */
 int dm_set_kernel_variant(dm_handle* h, int variant);
 

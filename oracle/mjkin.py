@@ -127,3 +127,45 @@ def motor_forces(model, ctrl):
     lo, hi = model.actuator_ctrlrange[:, 0], model.actuator_ctrlrange[:, 1]
     clipped = np.where(model.actuator_ctrllimited, np.clip(ctrl, lo, hi), ctrl)
     return model.actuator_gear * clipped
+
+
+def floor_contact_bits(model, d, rc):
+    """Floor contacts of the observation from kinematics alone: the contact word (bit 0 rfoot & floor, bit 1 lfoot &
+    floor, bits 2.. extra-contact geoms & floor) that get_foot_contact_obs / get_extra_contact_obs
+    (src/deepmimic_env.py:78-121) would read off mjdata.contact.  Restates MuJoCo 2.1's narrow phase for the only
+    pairs involved -- mjc_PlaneSphere: dist = (c - p0) . n - r;  mjc_PlaneBox: the box corners, i.e. the lowest one
+    decides -- with a contact reported iff dist <= margin, margin = max(geom_margin) of the pair (mj_collideGeoms),
+    after the contype / conaffinity filter.  PARITY UNPINNED: MuJoCo is not installable here."""
+    X = model.extra
+    fl = model.geom_name2id(rc["floor"])
+    assert X["geom_type"][fl] == "plane"
+    names = [rc["rfoot"], rc["lfoot"]] + list(rc["extra"] or [])
+    word = 0
+    for bit, name in enumerate(names):
+        g = model.geom_name2id(name)
+        if not ((model.geom_contype[fl] & model.geom_conaffinity[g]) or (model.geom_contype[g] & model.geom_conaffinity[fl])):
+            continue
+        b = model.geom_bodyid[g]
+        size = X["geom_size"][g]
+        if X["geom_type"][g] == "sphere":
+            dist = d.geom_xpos[g][2] - size[0]
+        elif X["geom_type"][g] == "box":
+            dist = d.geom_xpos[g][2] - float(np.abs(d.xmat[b][2]) @ np.asarray(size))
+        else:
+            raise NotImplementedError(X["geom_type"][g])
+        if dist <= max(X["geom_margin"][fl], X["geom_margin"][g]):
+            word |= 1 << bit
+    return word
+
+
+def floor_contact_dists(model, d, rc):
+    """The signed distances behind floor_contact_bits (tests use them to skip states sitting on the threshold)."""
+    X = model.extra
+    out = []
+    for name in [rc["rfoot"], rc["lfoot"]] + list(rc["extra"] or []):
+        g = model.geom_name2id(name)
+        b = model.geom_bodyid[g]
+        size = X["geom_size"][g]
+        z = d.geom_xpos[g][2]
+        out.append(z - size[0] if X["geom_type"][g] == "sphere" else z - float(np.abs(d.xmat[b][2]) @ np.asarray(size)))
+    return np.asarray(out)

@@ -32,6 +32,9 @@ struct DSink {
   void geom(int g, double x, double y, double z) { gx[3 * g] = x; gx[3 * g + 1] = y; gx[3 * g + 2] = z; }
 };
 
+static int g_contact_from_fk = 0;
+extern "C" void hh_set_contact_mode(int from_fk) { g_contact_from_fk = from_fk; }
+
 template <int KIND, class Rb>
 static int run(int n_clips, const dm_clip_t* clips, int n, const float* qpos, const float* qvel, const float* action,
                const uint32_t* contact, int* idx, int* ep_len, int* clip, float* obs, float* reward, uint8_t* done,
@@ -41,6 +44,7 @@ static int run(int n_clips, const dm_clip_t* clips, int n, const float* qpos, co
   int total;
   if (pack_clip_rows<Rb>(clips, n_clips, cs, rows, srows, total)) return -1;
   cs.rows = rows.data();
+  cs.contact_from_fk = g_contact_from_fk;
   using OL = ObsLayout<KIND, Rb>;
   for (int e = 0; e < n; ++e) {
     ArrayIO io{qpos + (size_t)e * Rb::NQ, qvel + (size_t)e * Rb::NV, action + (size_t)e * Rb::NA, obs + (size_t)e * OL::DIM,

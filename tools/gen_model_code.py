@@ -26,9 +26,11 @@ from deepmimic_mujoco_b200.mjcf import load_models  # noqa: E402
 
 ROBOT_CFG = {  # reference src/config.py:3-22
     "humanoid3d": dict(torso="chest", ee=["left_ankle", "right_ankle", "left_wrist", "right_wrist"], low_z=0.7,
-                       act_scale=1.0, n_hand=0),
+                       act_scale=1.0, n_hand=0, floor="floor", rfoot="right_ankle", lfoot="left_ankle", extra=[]),
     "unitree_g1": dict(torso="pelvis", ee=["left_foot", "right_foot", "left_hand", "right_hand"], low_z=0.4,
-                       act_scale=20.0, n_hand=14),
+                       act_scale=20.0, n_hand=14, floor="floor", rfoot="right_foot", lfoot="left_foot",
+                       extra=["left_foot_lheel", "left_foot_rheel", "left_foot_ltoe", "left_foot_rtoe",
+                              "right_foot_lheel", "right_foot_rheel", "right_foot_ltoe", "right_foot_rtoe"]),
 }
 
 
@@ -89,6 +91,20 @@ def emit_fk(m, cfg, e):
     chain = chain[::-1]
     assert chain[0] == 1 and m.jnt_type[m.body_jntadr[1]] == 0, "body 1 must carry the free joint"
     geoms_of = {i: [g for g in range(m.ngeom) if m.geom_bodyid[g] == i] for i in range(nb)}
+    # Floor contacts of the observation (deepmimic_env.py:78-121) from FK: MuJoCo's plane-sphere / plane-box narrow
+    # phase against the floor plane (z = 0, normal +z), contact iff dist <= margin with margin = max of the two geom
+    # margins (MuJoCo 2.1 mj_collideGeoms), and only for pairs that pass the contype / conaffinity filter.
+    # bit 0 rfoot, bit 1 lfoot, bits 2.. the extra-contact geoms.
+    X = m.extra
+    fl = m.geom_names.index(cfg["floor"])
+    assert X["geom_type"][fl] == "plane" and m.geom_bodyid[fl] == 0 and not np.any(m.geom_pos[fl]) and not X["geom_has_quat"][fl]
+    contact_slot = {}
+    for bit, name in enumerate([cfg["rfoot"], cfg["lfoot"]] + list(cfg["extra"])):
+        g = m.geom_names.index(name)
+        collide = (m.geom_contype[fl] & m.geom_conaffinity[g]) or (m.geom_contype[g] & m.geom_conaffinity[fl])
+        if collide:
+            assert not X["geom_has_quat"][g] and X["geom_type"][g] in ("sphere", "box"), name
+            contact_slot[g] = (bit, max(X["geom_margin"][fl], X["geom_margin"][g]))
 
     e("  // Forward kinematics + COM + torso cvel, unrolled for this tree (see file header).")
     e("  template <typename T, typename In, typename Sink>")
@@ -126,6 +142,16 @@ def emit_fk(m, cfg, e):
             ex = []
             for a, ax in enumerate("xyz"):
                 ex.append(" + ".join(["p%s_%d" % (ax, i)] + rows[a]))
+            if g in contact_slot:
+                bit, margin = contact_slot[g]
+                size = X["geom_size"][g]
+                R = Rn(i)
+                if X["geom_type"][g] == "sphere":
+                    dist = "(%s) - %s" % (ex[2], lit(size[0]))
+                else:  # box: the lowest of the 8 corners
+                    dist = "(%s) - (dm_abs(%s) * %s + dm_abs(%s) * %s + dm_abs(%s) * %s)" % (
+                        ex[2], R[2][0], lit(size[0]), R[2][1], lit(size[1]), R[2][2], lit(size[2]))
+                e("    if (%s <= %s) o.contact |= %du;  // floor & geom %d '%s'" % (dist, lit(margin), 1 << bit, g, m.geom_names[g]))
             if g in ee_geoms:
                 k = ee_geoms.index(g)
                 e("    o.ee[%d] = %s; o.ee[%d] = %s; o.ee[%d] = %s;  // geom %d '%s'"
@@ -136,6 +162,7 @@ def emit_fk(m, cfg, e):
         if i == torso:
             e("    o.tq[0] = qw_%d; o.tq[1] = qx_%d; o.tq[2] = qy_%d; o.tq[3] = qz_%d;" % ((i,) * 4))
 
+    e("    o.contact = 0u;")
     e("    T s1x = T(0), s1y = T(0), s1z = T(0);  // sum m * xpos")
     e("    T s2x = T(0), s2y = T(0), s2z = T(0);  // sum R * (m * ipos)")
     emit_body_tail(1)
