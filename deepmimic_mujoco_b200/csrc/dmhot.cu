@@ -38,6 +38,7 @@ struct dm_handle {
   // host-mode staging (the step's area doubles as the caller-visible pinned buffers of dm_host_buffers)
   Stage step_stage, reset_stage;
   cudaStream_t host_stream = nullptr;
+  cudaEvent_t obs_event = nullptr;
   // bookkeeping
   long long launches = 0;
   int variant = -1;  // -1 auto
@@ -131,6 +132,7 @@ extern "C" int dm_destroy(dm_handle* h) {
     if (st->h_pin) cudaFreeHost(st->h_pin);
   }
   for (auto& p : h->ev) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
+  if (h->obs_event) cudaEventDestroy(h->obs_event);
   if (h->host_stream) cudaStreamDestroy(h->host_stream);
   delete h;
   return DM_OK;
@@ -504,16 +506,35 @@ extern "C" int dm_step_host(dm_handle* h, const dm_step_args* a, int64_t* h2d_by
   // a buffer that already IS its staging slot (dm_host_buffers) needs no copy
   auto in = [](void* slot, const void* src, size_t bytes) { if (src != slot) { if (src) memcpy(slot, src, bytes); else memset(slot, 0, bytes); } };
   auto out = [](void* dst, const void* slot, size_t bytes) { if (dst && dst != slot) memcpy(dst, slot, bytes); };
-  in(g.hq, a->qpos, sizeof(float) * n * d.nq);
-  in(g.hv, a->qvel, sizeof(float) * n * d.nv);
-  in(g.ha, a->action, sizeof(float) * n * d.na);
-  in(g.hc, a->contact, 4 * n);
-  in(g.hi, a->idx, 4 * n);
-  in(g.hl, a->ep_len, 4 * n);
-  in(g.hk, a->clip, 4 * n);
-  if (a->ep_return) in(g.her, a->ep_return, 4 * n);
+  // Inputs that are not already in their staging slot are copied there one array at a time, each followed at once
+  // by its own H2D transfer, so the DMA of one array overlaps the host memcpy of the next; when every input is in
+  // place (dm_host_buffers) the whole input block goes in ONE transfer.
   const size_t in_bytes = g.out0;  // inputs + in-out state
-  CU(h, cudaMemcpyAsync(h->step_stage.d_mem, h->step_stage.h_pin, in_bytes, cudaMemcpyHostToDevice, s));
+  const bool in_place = a->qpos == g.hq && a->qvel == g.hv && a->action == g.ha && (const void*)a->contact == (const void*)g.hc &&
+                        a->idx == g.hi && a->ep_len == g.hl && (const void*)a->clip == (const void*)g.hk &&
+                        (!a->ep_return || a->ep_return == g.her);
+  if (in_place) {
+    CU(h, cudaMemcpyAsync(h->step_stage.d_mem, h->step_stage.h_pin, in_bytes, cudaMemcpyHostToDevice, s));
+  } else {
+    char* hb = (char*)h->step_stage.h_pin;
+    char* db = (char*)h->step_stage.d_mem;
+    auto ship = [&](const void* first, const void* last_end) -> cudaError_t {  // [first, last_end) of the pinned block
+      const size_t o0 = (const char*)first - hb, o1 = (const char*)last_end - hb;
+      return cudaMemcpyAsync(db + o0, hb + o0, o1 - o0, cudaMemcpyHostToDevice, s);
+    };
+    in(g.hq, a->qpos, sizeof(float) * n * d.nq);
+    CU(h, ship(g.hq, g.hq + n * d.nq));
+    in(g.hv, a->qvel, sizeof(float) * n * d.nv);
+    CU(h, ship(g.hv, g.hv + n * d.nv));
+    in(g.ha, a->action, sizeof(float) * n * d.na);
+    CU(h, ship(g.ha, g.ha + n * d.na));
+    in(g.hc, a->contact, 4 * n);
+    in(g.hi, a->idx, 4 * n);
+    in(g.hl, a->ep_len, 4 * n);
+    in(g.hk, a->clip, 4 * n);
+    if (a->ep_return) in(g.her, a->ep_return, 4 * n);
+    CU(h, ship(g.hc, hb + in_bytes));  // contact words + the in-out state block behind them
+  }
   dm_step_args k = *a;
   k.qpos = g.dq; k.qvel = g.dv; k.action = g.da; k.contact = g.dc; k.idx = g.di; k.ep_len = g.dl; k.clip = g.dk;
   k.obs = g.dob; k.reward = g.dr; k.done = g.dd; k.reason = g.dz; k.torque = a->torque ? g.dt : nullptr;
@@ -521,10 +542,21 @@ extern "C" int dm_step_host(dm_handle* h, const dm_step_args* a, int64_t* h2d_by
   rc = launch_step(h, &k, s);
   if (rc) return rc;
   const size_t back_bytes = g.end - g.state0;  // in-out state + outputs
-  CU(h, cudaMemcpyAsync((char*)h->step_stage.h_pin + g.state0, (char*)h->step_stage.d_mem + g.state0, back_bytes,
-                        cudaMemcpyDeviceToHost, s));
-  CU(h, cudaStreamSynchronize(s));
-  out(a->obs, g.ho, sizeof(float) * n * d.obs_dim);
+  char* hb2 = (char*)h->step_stage.h_pin;
+  char* db2 = (char*)h->step_stage.d_mem;
+  if (a->obs == g.ho) {  // outputs stay in the pinned block: one transfer
+    CU(h, cudaMemcpyAsync(hb2 + g.state0, db2 + g.state0, back_bytes, cudaMemcpyDeviceToHost, s));
+    CU(h, cudaStreamSynchronize(s));
+  } else {  // two transfers: the caller's observation copy overlaps the DMA of the remaining outputs
+    const size_t obs_end = (size_t)((char*)(g.ho + n * d.obs_dim) - hb2);
+    if (!h->obs_event) CU(h, cudaEventCreateWithFlags(&h->obs_event, cudaEventDisableTiming));
+    CU(h, cudaMemcpyAsync(hb2 + g.state0, db2 + g.state0, obs_end - g.state0, cudaMemcpyDeviceToHost, s));
+    CU(h, cudaEventRecord(h->obs_event, s));
+    CU(h, cudaMemcpyAsync(hb2 + obs_end, db2 + obs_end, g.end - obs_end, cudaMemcpyDeviceToHost, s));
+    CU(h, cudaEventSynchronize(h->obs_event));
+    memcpy(a->obs, g.ho, sizeof(float) * n * d.obs_dim);
+    CU(h, cudaStreamSynchronize(s));
+  }
   out(a->reward, g.hr, 4 * n);
   out(a->done, g.hd, n);
   out(a->reason, g.hz, n);

@@ -150,9 +150,14 @@ class DPVecEnv:
 
     @staticmethod
     def _into(dst, src):
-        """src -> the pinned array dst (no-op when the caller already wrote into dst)."""
-        if src is not dst:
-            np.copyto(dst, src, casting="unsafe")
+        """The array to hand to dm_step_host for the pinned slot dst: dst itself when the caller already wrote into it;
+        the caller's array when the library can read it as it is (C-contiguous, right dtype and shape -- the copy into
+        the pinned block then happens inside dm_step_host, pipelined with the H2D transfers); else a converted copy in dst."""
+        if src is dst:
+            return dst
+        if isinstance(src, np.ndarray) and src.dtype == dst.dtype and src.shape == dst.shape and src.flags.c_contiguous:
+            return src
+        np.copyto(dst, src, casting="unsafe")
         return dst
 
     def step_wait(self):
@@ -168,11 +173,16 @@ class DPVecEnv:
             raise N.DmError("DPVecEnv.step needs force_state=(qpos, qvel[, contact]) or a physics callback: MuJoCo's "
                             "mj_step is outside this package")
         assert np.shape(fs[0]) == p["qpos"].shape and np.shape(fs[1]) == p["qvel"].shape
-        self.qpos, self.qvel = self._into(p["qpos"], fs[0]), self._into(p["qvel"], fs[1])
+        qpos_in, qvel_in = self._into(p["qpos"], fs[0]), self._into(p["qvel"], fs[1])
         if len(fs) > 2 and fs[2] is not None:
             contact = self._into(p["contact"], fs[2])
-        h2d, d2h = self.hp.step_host(n, self.qpos, self.qvel, self._actions, contact, self.idx, self.ep_len, self.clip,
-                                     self.obs, self.reward, self.done, self.reason, self.torque, self.terms, self.ep_return)
+        # copy_outputs: the observation goes straight into a fresh caller-owned array (copied inside dm_step_host while
+        # the remaining outputs are still in flight); self.obs then aliases it until the next step
+        out_obs = np.empty_like(p["obs"]) if self.copy_outputs else p["obs"]
+        self.obs = out_obs
+        h2d, d2h = self.hp.step_host(n, qpos_in, qvel_in, self._actions, contact, self.idx, self.ep_len, self.clip,
+                                     out_obs, self.reward, self.done, self.reason, self.torque, self.terms, self.ep_return)
+        self.qpos, self.qvel, self._actions = p["qpos"], p["qvel"], p["action"]  # the pinned copies, never the caller's arrays
         self.h2d_bytes, self.d2h_bytes = h2d, d2h
         dones = self.done.view(np.bool_)
         infos = LazyInfos(n)
@@ -181,6 +191,7 @@ class DPVecEnv:
                 if self.reason[i] != 8:
                     infos[i].update({k: float(self.terms[i, j]) for j, k in enumerate(N.TERM_NAMES[:5])})
         rews = self.reward.copy() if self.copy_outputs else self.reward
+        obs_out = out_obs if self.copy_outputs else self.obs
         if dones.any():
             dones = dones.copy()
             ids = np.nonzero(dones)[0]
@@ -198,7 +209,7 @@ class DPVecEnv:
                 info["episode"] = {"r": float(ep_ret[k]), "l": int(ep_len[k])}
         elif self.copy_outputs:
             dones = dones.copy()
-        return (self.obs.copy() if self.copy_outputs else self.obs), rews, dones, infos
+        return obs_out, rews, dones, infos
 
     def step(self, actions, force_state=None):
         self.step_async(actions, force_state)
