@@ -26,6 +26,11 @@ sys.path.insert(0, REPO)
 
 BYTES_PER_ENV_STEP = {("humanoid3d", 0): 793, ("unitree_g1", 0): 953, ("unitree_g1", 1): 1021}
 L2_BYTES = 126e6
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE step-kernel launch from `ncu --set full` captures of this very
+# command (profiles/r01_step_tile_v3_*_ncu_full_summary.txt), keyed by (robot, env kind, envs per GPU); at 4096 envs the
+# 1.7 MB of outputs are still dirty in L2 when the kernel ends, so only the reads reach DRAM inside the launch
+NCU_TRAFFIC = {("humanoid3d", 0, 4096): (1.764864e6, "profiles/r01_step_tile_v3_4096_ncu_full_summary.txt"),
+               ("humanoid3d", 0, 1048576): (430.431744e6 + 365.887744e6, "profiles/r01_step_tile_v3_1M_ncu_full_summary.txt")}
 
 
 def parse():
@@ -458,7 +463,8 @@ def main():
     bytes_per_launch = wl.bpe * args.envs
     ach = bytes_per_launch / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
     roof = {"bound": "hbm", "kernel": "step kernel (K1)", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-            "traffic": None, "peak_source": peak_src, "bytes_per_env_step": wl.bpe, "envs_per_launch": args.envs,
+            "traffic": NCU_TRAFFIC.get((wl.hp.robot, wl.kind, args.envs), (None, None))[0],
+            "traffic_source": NCU_TRAFFIC.get((wl.hp.robot, wl.kind, args.envs), (None, None))[1], "peak_source": peak_src, "bytes_per_env_step": wl.bpe, "envs_per_launch": args.envs,
             "kernel_ms": k_ms, "kernel_launches_timed": k_n}
 
     line = {"metric": "env-steps/s (ref-lookup+FK+reward+obs+PD)", "value": value, "unit": "env-steps/s", "n_gpus": world,
