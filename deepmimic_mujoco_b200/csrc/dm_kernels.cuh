@@ -102,6 +102,7 @@ struct TableIO {
 };
 struct TableSink {
   static constexpr bool kWantsGeoms = true;
+  __device__ static constexpr bool contact_on() { return false; }
   double* bx;
   double* gx;
   __device__ __forceinline__ void body(int i, double x, double y, double z) {
@@ -173,6 +174,14 @@ struct ResetIO {
   __device__ __forceinline__ void tau(int, float) {}
 };
 
+struct ResetSink {  // FK sink of the reset observation: only the floor-contact switch
+  static constexpr bool kWantsGeoms = false;
+  bool want_contact;
+  __device__ __forceinline__ bool contact_on() const { return want_contact; }
+  template <typename T> __device__ __forceinline__ void body(int, T, T, T) {}
+  template <typename T> __device__ __forceinline__ void geom(int, T, T, T) {}
+};
+
 template <int KIND, class Rb>
 __global__ void __launch_bounds__(128) reset_kernel(const __grid_constant__ ResetParams p) {
   using OL = ObsLayout<KIND, Rb>;
@@ -224,7 +233,7 @@ __global__ void __launch_bounds__(128) reset_kernel(const __grid_constant__ Rese
     for (int j = 0; j < OL::DIM; ++j) t[j * p.es] = io.ob[j * p.es];
   }
   FkOut<float> fk;
-  NullSink sink;
+  ResetSink sink{p.cs.contact_from_fk != 0};
   Rb::template fk<float>(io, fk, sink);
   float root_rpy[3];
   dm_rpy_raw(io.qpos(3), io.qpos(4), io.qpos(5), io.qpos(6), root_rpy[0], root_rpy[1], root_rpy[2]);

@@ -28,6 +28,7 @@ struct FkOut {
 
 struct NullSink {
   static constexpr bool kWantsGeoms = false;
+  DM_HD static constexpr bool contact_on() { return false; }  // floor-contact tests of the FK (DM_CONTACT_FROM_FK)
   template <typename T> DM_HD void body(int, T, T, T) {}
   template <typename T> DM_HD void geom(int, T, T, T) {}
 };

@@ -176,6 +176,8 @@ struct EeSink {
   static constexpr bool kWantsGeoms = false;
   const float* __restrict__ tgt;  // the frame's 4 x 3 target positions (RowLayout::EE)
   float e2;
+  bool want_contact;  // run the floor-contact tests of the FK (DM_CONTACT_FROM_FK)
+  DM_HD bool contact_on() const { return want_contact; }
   template <typename T> DM_HD void body(int, T, T, T) {}
   DM_HD void geom(int g, float x, float y, float z) {  // g is a literal in the generated code
 #pragma unroll
@@ -261,7 +263,7 @@ DM_HD void env_step(IO& io, const ClipSet& cs, const float* __restrict__ rows, E
   write_torque<Rb>(io);
 
   FkOut<float> fk;
-  EeSink<Rb> sink{row + RL::EE, 0.0f};
+  EeSink<Rb> sink{row + RL::EE, 0.0f, cs.contact_from_fk != 0};
   Rb::template fk<float>(io, fk, sink);
 
   if (cs.contact_from_fk) contact = fk.contact;

@@ -92,7 +92,11 @@ __device__ __forceinline__ T ld_stream(const T* p) {
 template <int KIND, class Rb>
 struct TileCfg {
   using OL = ObsLayout<KIND, Rb>;
-  static constexpr int TE = 128;                       // environments per tile = threads per group
+#ifndef DM_TE
+#define DM_TE 128
+#endif
+  static constexpr int TE = DM_TE;                     // environments per tile = threads per group
+  static constexpr int NW = TE / 32;                   // warps per group
   static constexpr int NCOMP = OL::DIM - 2 * Rb::NJ;  // computed obs entries (torso, contacts, phase, player action)
   // a tile buffer row: the input rows (nq + nv floats), later the observation row plus one statistics column (reward)
   static constexpr int ROW = (Rb::NQ + Rb::NV) > OL::DIM + 1 ? (Rb::NQ + Rb::NV) : OL::DIM + 1;
@@ -100,7 +104,7 @@ struct TileCfg {
   static constexpr int BUF_FLOATS = TE * ROW;
   static constexpr size_t BUF_BYTES = sizeof(float) * BUF_FLOATS;              // one ring slot
   static constexpr size_t ACC_BYTES = sizeof(double) * (2 * NCOLIT * TE + 4);  // per group, STATS only
-  static constexpr int MAXBUF = 6;                                             // ring slots (mbarriers 0 .. MAXBUF-1, table = MAXBUF)
+  static constexpr int MAXBUF = 12;                                            // ring slots (mbarriers 0 .. MAXBUF-1, table = MAXBUF)
   static constexpr int NUP = (Rb::NU + 3) / 4 * 4;
   static constexpr size_t FIXED_BYTES = 128 + sizeof(float) * 3 * NUP;  // mbarriers + motor table (gear | lo | hi)
   static_assert(FIXED_BYTES % 16 == 0 && BUF_BYTES % 128 == 0, "alignment");
@@ -127,11 +131,11 @@ struct TileIO {
 // groups per CTA the kernel is compiled for (register budget = 65536 / (128 G) per thread)
 template <class Rb>
 struct KernelGroups {  // measured on humanoid3d: G = 5 (96 registers, ~330 B of spills) is 40 % slower than G = 4
-  static constexpr int G = 4;
+  static constexpr int G = 4 * 128 / DM_TE;
 };
 template <>
 struct KernelGroups<Robot_unitree_g1> {  // 37 hinges: the joint blocks alone are 74 live registers when the tile is written
-  static constexpr int G = 3;  // measured at 1 M envs: G = 3 (168 regs) 407 us, G = 2 (254 regs, no spills) 484 us, G = 4 (128 regs) 462 us
+  static constexpr int G = 3 * 128 / DM_TE;  // measured at 1 M envs: G = 3 (168 regs) 407 us, G = 2 (254 regs, no spills) 484 us, G = 4 (128 regs) 462 us
 };
 
 struct TileExtra {
@@ -142,12 +146,12 @@ struct TileExtra {
   int skip_compute;  // experiment: memory skeleton only (no env_step)
 };
 
-__device__ __forceinline__ void group_sync(int group) {  // named barrier 1 + group, 128 threads
-  asm volatile("bar.sync %0, 128;" ::"r"(group + 1) : "memory");
+__device__ __forceinline__ void group_sync(int group) {  // named barrier 1 + group, one group of threads
+  asm volatile("bar.sync %0, %1;" ::"r"(group + 1), "n"(DM_TE) : "memory");
 }
 
 template <int KIND, class Rb, bool TERMS, bool STATS, bool TABLE_SMEM, int G>
-__global__ void __launch_bounds__(128 * G, 1) step_tile_kernel(const __grid_constant__ StepParams p, const TileExtra x) {
+__global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_constant__ StepParams p, const TileExtra x) {
   using OL = ObsLayout<KIND, Rb>;
   using TC = TileCfg<KIND, Rb>;
   constexpr int TE = TC::TE, NJ = Rb::NJ, DIM = OL::DIM, NCOMP = TC::NCOMP, NCOLIT = TC::NCOLIT;
@@ -367,9 +371,9 @@ __global__ void __launch_bounds__(128 * G, 1) step_tile_kernel(const __grid_cons
         const int c = it * 32 + lane;
         if (c <= DIM) {  // column DIM is the reward
           const float* src = c < DIM ? buf + warp * DIM + c : s_rw + warp;
-          const int stride = c < DIM ? 4 * DIM : 4;
+          const int stride = c < DIM ? TC::NW * DIM : TC::NW;
 #pragma unroll 8
-          for (int r = 0; r < TE / 4; ++r) {
+          for (int r = 0; r < TE / TC::NW; ++r) {
             const float v = src[r * stride];
             cs32[it] += v;
             css32[it] = fmaf(v, v, css32[it]);
@@ -400,7 +404,7 @@ __global__ void __launch_bounds__(128 * G, 1) step_tile_kernel(const __grid_cons
       const int it = c >> 5, ln = c & 31;
       double v = 0.0;
       for (int g = 0; g < n_groups; ++g)
-        for (int w = 0; w < 4; ++w) v += acc0[(size_t)g * GS + ((sq ? NCOLIT : 0) + it) * TE + w * 32 + ln];
+        for (int w = 0; w < TC::NW; ++w) v += acc0[(size_t)g * GS + ((sq ? NCOLIT : 0) + it) * TE + w * 32 + ln];
       return v;
     };
     auto donesum = [&](int k) {

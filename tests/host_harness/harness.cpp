@@ -27,6 +27,7 @@ struct DIO {
 };
 struct DSink {
   static constexpr bool kWantsGeoms = true;
+  static constexpr bool contact_on() { return false; }
   double *bx, *gx;
   void body(int i, double x, double y, double z) { bx[3 * i] = x; bx[3 * i + 1] = y; bx[3 * i + 2] = z; }
   void geom(int g, double x, double y, double z) { gx[3 * g] = x; gx[3 * g + 1] = y; gx[3 * g + 2] = z; }

@@ -151,7 +151,7 @@ def emit_fk(m, cfg, e):
                 else:  # box: the lowest of the 8 corners
                     dist = "(%s) - (dm_abs(%s) * %s + dm_abs(%s) * %s + dm_abs(%s) * %s)" % (
                         ex[2], R[2][0], lit(size[0]), R[2][1], lit(size[1]), R[2][2], lit(size[2]))
-                e("    if (%s <= %s) o.contact |= %du;  // floor & geom %d '%s'" % (dist, lit(margin), 1 << bit, g, m.geom_names[g]))
+                e("    if (sink.contact_on() && %s <= %s) o.contact |= %du;  // floor & geom %d '%s'" % (dist, lit(margin), 1 << bit, g, m.geom_names[g]))
             if g in ee_geoms:
                 k = ee_geoms.index(g)
                 e("    o.ee[%d] = %s; o.ee[%d] = %s; o.ee[%d] = %s;  // geom %d '%s'"
