@@ -32,6 +32,12 @@ class Clip(C.Structure):
                 ("qpos", C.c_void_p), ("qvel", C.c_void_p), ("body_xpos", C.c_void_p), ("geom_xpos", C.c_void_p)]
 
 
+class RawClip(C.Structure):
+    _fields_ = [("n_frames", C.c_int32), ("n_cols", C.c_int32), ("direct_qpos", C.c_int32), ("getup", C.c_int32),
+                ("flags", C.c_int32), ("fixed_row", C.c_int32), ("virtual_len", C.c_int32), ("same_as", C.c_int32),
+                ("frames", C.c_void_p)]
+
+
 class StepArgs(C.Structure):
     _fields_ = [("n", C.c_int32), ("layout", C.c_int32), ("ld", C.c_int64),
                 ("qpos", C.c_void_p), ("qvel", C.c_void_p), ("action", C.c_void_p), ("contact", C.c_void_p),
@@ -52,7 +58,7 @@ class ResetArgs(C.Structure):
 
 # every symbol include/dmhot.h declares (tests check that the library exports each one)
 SYMBOLS = ["dm_abi_version", "dm_create", "dm_destroy", "dm_last_error", "dm_get_dims", "dm_get_model", "dm_fk_tables",
-           "dm_upload_clips", "dm_get_packed_rows", "dm_step", "dm_reset", "dm_step_host", "dm_reset_host", "dm_host_buffers",
+           "dm_upload_clips", "dm_compile_clips", "dm_get_compiled_clip", "dm_get_packed_rows", "dm_step", "dm_reset", "dm_step_host", "dm_reset_host", "dm_host_buffers",
            "dm_stats_zero", "dm_stats_device_ptr", "dm_stats_read", "dm_launch_count", "dm_step_kernel_time",
            "dm_set_timing", "dm_set_kernel_variant", "dm_set_contact_mode"]
 
@@ -76,6 +82,8 @@ def lib():
     L.dm_get_model.argtypes = [C.c_void_p] + [C.c_void_p] * 7
     L.dm_fk_tables.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.dm_upload_clips.argtypes = [C.c_void_p, C.c_int32, C.POINTER(Clip)]
+    L.dm_compile_clips.argtypes = [C.c_void_p, C.c_int32, C.POINTER(RawClip)]
+    L.dm_get_compiled_clip.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_double)] + [C.c_void_p] * 4
     L.dm_get_packed_rows.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32)]
     L.dm_step.argtypes = [C.c_void_p, C.POINTER(StepArgs)]
     L.dm_reset.argtypes = [C.c_void_p, C.POINTER(ResetArgs)]

@@ -10,6 +10,7 @@
 #include <cuda_runtime.h>
 
 #include "dm_step.cuh"
+#include "dm_fk_table.cuh"
 #include "generated/robot_humanoid3d.cuh"
 #include "generated/robot_unitree_g1.cuh"
 
@@ -91,39 +92,6 @@ __global__ void __launch_bounds__(128) step_strided_kernel(const __grid_constant
     env_step<KIND, Rb, StridedIO, TERMS>(io, p.cs, p.cs.rows, st, contact, so);
     finish_env<KIND, Rb, TERMS>(p, env, st, so);
   }
-}
-
-// ---- K3: float64 FK of key frames --------------------------------------------------------------
-struct TableIO {
-  const double* qp;
-  const double* qv;
-  __device__ __forceinline__ double qpos(int j) const { return qp[j]; }
-  __device__ __forceinline__ double qvel(int j) const { return qv[j]; }
-};
-struct TableSink {
-  static constexpr bool kWantsGeoms = true;
-  __device__ static constexpr bool contact_on() { return false; }
-  double* bx;
-  double* gx;
-  __device__ __forceinline__ void body(int i, double x, double y, double z) {
-    bx[3 * i] = x; bx[3 * i + 1] = y; bx[3 * i + 2] = z;
-  }
-  __device__ __forceinline__ void geom(int g, double x, double y, double z) {
-    gx[3 * g] = x; gx[3 * g + 1] = y; gx[3 * g + 2] = z;
-  }
-};
-
-template <class Rb>
-__global__ void fk_table_kernel(int n, const double* qpos, const double* qvel, double* body_xpos, double* geom_xpos) {
-  const int f = blockIdx.x * blockDim.x + threadIdx.x;
-  if (f >= n) return;
-  TableIO in{qpos + (size_t)f * Rb::NQ, qvel + (size_t)f * Rb::NV};
-  TableSink sink{body_xpos + (size_t)f * Rb::NBODY * 3, geom_xpos + (size_t)f * Rb::NGEOM * 3};
-  // world body and its geoms (the floor plane at the origin)
-  sink.body(0, 0.0, 0.0, 0.0);
-  for (int g = 0; g < Rb::NGEOM; ++g) sink.geom(g, 0.0, 0.0, 0.0);
-  FkOut<double> o;
-  Rb::template fk<double>(in, o, sink);
 }
 
 // ---- K2: reset -----------------------------------------------------------------------------------

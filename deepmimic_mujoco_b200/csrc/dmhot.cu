@@ -12,6 +12,7 @@
 #include "dm_kernels.cuh"
 #include "dm_tile_kernel.cuh"
 #include "dm_pack.h"
+#include "dm_clip_compiler.h"
 
 using namespace dm;
 
@@ -32,6 +33,8 @@ struct dm_handle {
   float* d_state_rows = nullptr;  // [total_rows, nq + nv]
   std::vector<float> h_rows;
   int total_rows = 0;
+  std::vector<CompiledClip> compiled;  // float64 device tables of dm_compile_clips (entries of same_as clips are empty)
+  std::vector<int> compiled_src;       // clip -> index into `compiled` that holds its tables
   ClipSet cs{};
   // statistics
   double* d_stats = nullptr;
@@ -127,6 +130,7 @@ extern "C" int dm_destroy(dm_handle* h) {
   cudaFree(h->d_rows);
   cudaFree(h->d_state_rows);
   cudaFree(h->d_stats);
+  for (auto& c : h->compiled) free_compiled_clip(&c);
   for (Stage* st : {&h->step_stage, &h->reset_stage}) {
     cudaFree(st->d_mem);
     if (st->h_pin) cudaFreeHost(st->h_pin);
@@ -220,8 +224,97 @@ extern "C" int dm_upload_clips(dm_handle* h, int32_t n_clips, const dm_clip_t* c
     h->cs = cs;
     h->total_rows = total;
     h->h_rows.swap(rows);
+    for (auto& c : h->compiled) free_compiled_clip(&c);
+    h->compiled.clear();
+    h->compiled_src.clear();
     return DM_OK;
   });
+}
+
+// The same tables, built on the device from the raw "Frames" rows (dm_clip_compiler.cu).
+extern "C" int dm_compile_clips(dm_handle* h, int32_t n_clips, const dm_raw_clip_t* raw) {
+  if (!h || !raw || n_clips <= 0 || n_clips > DM_MAX_CLIPS) return fail(h, DM_E_ARG, "dm_compile_clips: need 1..%d clips", DM_MAX_CLIPS);
+  if (h->kind == DM_ENV_COMBINED && n_clips != 4)
+    return fail(h, DM_E_ARG, "dm_compile_clips: DPCombinedEnv needs exactly 4 clips (walk, run, getup, to_getup)");
+  CU(h, cudaSetDevice(h->device));
+  std::vector<CompiledClip> comp(n_clips);
+  std::vector<int> src(n_clips);
+  auto drop = [&] { for (auto& c : comp) free_compiled_clip(&c); };
+  for (int c = 0; c < n_clips; ++c) {
+    const dm_raw_clip_t& r = raw[c];
+    if (r.same_as >= 0) {
+      if (r.same_as >= c || raw[r.same_as].same_as >= 0) { drop(); return fail(h, DM_E_ARG, "dm_compile_clips: clip %d: same_as must name an earlier compiled clip", c); }
+      src[c] = r.same_as;
+      continue;
+    }
+    src[c] = c;
+    if (!r.frames || r.n_frames <= 0 || r.n_cols < 2) { drop(); return fail(h, DM_E_ARG, "dm_compile_clips: clip %d has no frames", c); }
+    double* d_frames = nullptr;
+    const size_t bytes = sizeof(double) * (size_t)r.n_frames * r.n_cols;
+    if (cudaMalloc(&d_frames, bytes) != cudaSuccess || cudaMemcpy(d_frames, r.frames, bytes, cudaMemcpyHostToDevice) != cudaSuccess) {
+      cudaFree(d_frames); drop();
+      return fail(h, DM_E_CUDA, "dm_compile_clips: upload of clip %d: %s", c, cudaGetErrorString(cudaGetLastError()));
+    }
+    const char* bad = compile_clip_device(h->robot, d_frames, r.n_frames, r.n_cols, r.direct_qpos, r.getup, r.frames[0], &comp[c],
+                                          &h->launches, h->host_stream);
+    cudaFree(d_frames);
+    if (bad) { drop(); return fail(h, DM_E_ARG, "dm_compile_clips: clip %d: %s", c, bad); }
+  }
+  ClipSet cs{};
+  cs.n_clips = n_clips;
+  int total = 0;
+  for (int c = 0; c < n_clips; ++c) {
+    const dm_raw_clip_t& r = raw[c];
+    const int n_rows = comp[src[c]].len;
+    if (r.fixed_row >= n_rows || (r.fixed_row >= 0 && r.virtual_len <= 0)) { drop(); return fail(h, DM_E_ARG, "dm_compile_clips: clip %d: fixed_row / virtual_len inconsistent", c); }
+    cs.clip[c] = ClipDesc{total, r.fixed_row >= 0 ? r.virtual_len : n_rows, r.flags, r.fixed_row};
+    total += n_rows;
+  }
+  const size_t stride = h->dims.row_stride, sstride = h->dims.nq + h->dims.nv;
+  float *d_rows = nullptr, *d_srows = nullptr;
+  if (cudaMalloc(&d_rows, sizeof(float) * total * stride) != cudaSuccess || cudaMalloc(&d_srows, sizeof(float) * total * sstride) != cudaSuccess) {
+    cudaFree(d_rows); cudaFree(d_srows); drop();
+    return fail(h, DM_E_NOMEM, "dm_compile_clips: %s", cudaGetErrorString(cudaGetLastError()));
+  }
+  for (int c = 0; c < n_clips; ++c) {
+    const CompiledClip& k = comp[src[c]];
+    const char* bad = pack_rows_device(h->robot, k, 0, k.len, cs.clip[c].row0, d_rows, d_srows, &h->launches, h->host_stream);
+    if (bad) { cudaFree(d_rows); cudaFree(d_srows); drop(); return fail(h, DM_E_CUDA, "dm_compile_clips: %s", bad); }
+  }
+  std::vector<float> rows((size_t)total * stride);
+  cudaError_t e = cudaMemcpyAsync(rows.data(), d_rows, rows.size() * sizeof(float), cudaMemcpyDeviceToHost, h->host_stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(h->host_stream);
+  if (e != cudaSuccess) { cudaFree(d_rows); cudaFree(d_srows); drop(); return fail(h, DM_E_CUDA, "dm_compile_clips: %s", cudaGetErrorString(e)); }
+  cudaFree(h->d_rows);
+  cudaFree(h->d_state_rows);
+  for (auto& c : h->compiled) free_compiled_clip(&c);
+  h->d_rows = d_rows;
+  h->d_state_rows = d_srows;
+  cs.rows = d_rows;
+  h->cs = cs;
+  h->total_rows = total;
+  h->h_rows.swap(rows);
+  h->compiled.swap(comp);
+  h->compiled_src.swap(src);
+  return DM_OK;
+}
+
+extern "C" int dm_get_compiled_clip(const dm_handle* h, int32_t clip, int32_t* len, double* dt, double* qpos, double* qvel,
+                                    double* body_xpos, double* geom_xpos) {
+  if (!h) return fail(nullptr, DM_E_ARG, "dm_get_compiled_clip: NULL handle");
+  dm_handle* hm = const_cast<dm_handle*>(h);
+  if (clip < 0 || clip >= (int)h->compiled_src.size()) return fail(hm, DM_E_STATE, "dm_get_compiled_clip: clip %d was not built by dm_compile_clips", clip);
+  const CompiledClip& c = h->compiled[h->compiled_src[clip]];
+  if (len) *len = c.len;
+  if (dt) *dt = c.dt;
+  CU(hm, cudaSetDevice(h->device));
+  const dm_dims_t& d = h->dims;
+  const size_t n = c.len;
+  if (qpos) CU(hm, cudaMemcpy(qpos, c.qpos, sizeof(double) * n * d.nq, cudaMemcpyDeviceToHost));
+  if (qvel) CU(hm, cudaMemcpy(qvel, c.qvel, sizeof(double) * n * d.nv, cudaMemcpyDeviceToHost));
+  if (body_xpos) CU(hm, cudaMemcpy(body_xpos, c.body_xpos, sizeof(double) * n * d.nbody * 3, cudaMemcpyDeviceToHost));
+  if (geom_xpos) CU(hm, cudaMemcpy(geom_xpos, c.geom_xpos, sizeof(double) * n * d.ngeom * 3, cudaMemcpyDeviceToHost));
+  return DM_OK;
 }
 
 extern "C" int dm_get_packed_rows(const dm_handle* h, float* rows, int32_t* total_rows) {

@@ -99,20 +99,60 @@ class HotPath:
         self._keep = keep
         return self
 
+    def compile_clips(self, clips, flags, names=None, transition=None):
+        """The device clip compiler (dm_compile_clips): `clips` are parsed motion files as assets.load_clip returns
+        them (dict(frames=float64 [n, cols], format, loop, name)); the tables are built and packed on the GPU.
+        transition = (target_index, virtual_len, frame): appends a MotionTransition clip sharing the target's tables."""
+        n = len(clips) + (1 if transition else 0)
+        raw = (N.RawClip * n)()
+        keep = []
+        for i, c in enumerate(clips):
+            fr = np.ascontiguousarray(c["frames"], dtype=np.float64)
+            keep.append(fr)
+            raw[i] = N.RawClip(fr.shape[0], fr.shape[1], 1 if c.get("format") else 0, 1 if "getup" in c["name"] else 0,
+                               int(flags[i]), -1, 0, -1, N.np_ptr(fr))
+        if transition:
+            t, vlen, frame = transition
+            raw[n - 1] = N.RawClip(0, 0, 0, 0, 0, int(frame), int(vlen), int(t), None)
+        N.check(self.L.dm_compile_clips(self.h, n, raw), self.h, "dm_compile_clips")
+        self.clip_names = list(names) if names else [c["name"] for c in clips] + (["transition"] if transition else [])
+        self.clip_lens = []
+        for i in range(n):
+            ln = C.c_int32()
+            N.check(self.L.dm_get_compiled_clip(self.h, i, C.byref(ln), None, None, None, None, None), self.h, "dm_get_compiled_clip")
+            self.clip_lens.append(int(transition[1]) if transition and i == n - 1 else ln.value)
+        self._keep = None
+        return self
+
+    def compiled_clip(self, i):
+        """float64 tables of clip i as built by the device compiler -> dict(dt, qpos, qvel, body_xpos, geom_xpos)."""
+        ln, dt = C.c_int32(), C.c_double()
+        N.check(self.L.dm_get_compiled_clip(self.h, i, C.byref(ln), C.byref(dt), None, None, None, None), self.h, "dm_get_compiled_clip")
+        d, L = self.dims, ln.value
+        out = dict(qpos=np.zeros((L, d.nq)), qvel=np.zeros((L, d.nv)), body_xpos=np.zeros((L, d.nbody, 3)),
+                   geom_xpos=np.zeros((L, d.ngeom, 3)))
+        N.check(self.L.dm_get_compiled_clip(self.h, i, None, None, *[N.np_ptr(out[k]) for k in
+                                                                       ("qpos", "qvel", "body_xpos", "geom_xpos")]),
+                self.h, "dm_get_compiled_clip")
+        out["dt"] = dt.value
+        return out
+
+    def _load(self, motions, flags, names, transition=None):
+        from . import assets
+        from .mocap import MocapDM
+        clips = [assets.load_clip(self.robot, m) for m in motions]
+        self.compile_clips(clips, flags, names, transition)
+        self.mocaps = [MocapDM(self.robot, hotpath=self)._adopt(c, self, i) for i, c in enumerate(clips)]
+        return self
+
     def load_motions(self, motions):
         """DPEnv semantics: one clip per motion name (per-env clip ids select among them)."""
-        from .mocap import MocapDM
-        mocaps = [MocapDM(self.robot, hotpath=self).load_motion(m) for m in motions]
-        self.mocaps = mocaps
-        return self.upload_mocaps(mocaps, [clip_flags(self.robot, m) for m in motions], list(motions))
+        return self._load(motions, [clip_flags(self.robot, m) for m in motions], list(motions))
 
     def load_combined(self):
         """DPCombinedEnv: walk, run, getup_facedown_towalk + MTToGetup (combined_env.py:167-178)."""
-        from .mocap import MocapDM
         motions = ["walk", "run", "getup_facedown_towalk"]
-        mocaps = [MocapDM(self.robot, hotpath=self).load_motion(m) for m in motions]
-        self.mocaps = mocaps
-        return self.upload_mocaps(mocaps, [0, 0, 0], motions + ["to_getup"], transition=(2, 180, 1))
+        return self._load(motions, [0, 0, 0], motions + ["to_getup"], transition=(2, 180, 1))
 
     def packed_rows(self):
         n = C.c_int32()

@@ -142,6 +142,29 @@ int dm_fk_tables(dm_handle* h, int32_t n, const double* qpos, const double* qvel
 /* pack + upload the clip tables (replaces the per-process MocapDM objects a step indexes:
  * mocap.get_qpos/get_qvel/get_geom_xpos/get_body_xpos, src/mujoco/mocap_v2.py:338-348) */
 int dm_upload_clips(dm_handle* h, int32_t n_clips, const dm_clip_t* clips);
+/* Raw mocap clip = the parsed "Frames" array of a DeepMimic motion file (src/mujoco/motions/*.txt), float64, HOST.
+ * same_as >= 0 reuses the compiled tables of that earlier clip of the same call (the MotionTransition pose source,
+ * src/combined_env.py:67-99) and ignores frames. */
+typedef struct {
+  int32_t n_frames, n_cols;  /* 44 columns for DeepMimic rows (humanoid3d), nq + 1 for "Format": "direct_qpos" */
+  int32_t direct_qpos;       /* "Format" == "direct_qpos"            src/mujoco/mocap_v2.py:49-51,271-272 */
+  int32_t getup;             /* "getup" in the file path: VMX = 5    src/mujoco/mocap_v2.py:156-158 */
+  int32_t flags;             /* DM_CLIP_* */
+  int32_t fixed_row;         /* as dm_clip_t */
+  int32_t virtual_len;       /* get_length() of a fixed_row clip; ignored otherwise */
+  int32_t same_as;           /* -1, or an earlier clip index */
+  const double* frames;      /* [n_frames, n_cols]; frames[0] of each row is the frame duration */
+} dm_raw_clip_t;
+/* The clip compiler on the device: MocapDM.read_raw_data (src/mujoco/mocap_v2.py:33-336: axis alignment, Euler
+ * conversion, the shoulder / hip continuity fix, finite-difference velocities, FK of every key frame, x k resampling
+ * to the simulator step) in float64 CUDA kernels, followed by the fp32 packing of dm_upload_clips -- the tables never
+ * visit the host.  Replaces dm_upload_clips(MocapDM tables); fails with the reference's message for clips whose frame
+ * duration is not a multiple of the simulator step (backflip, spin). */
+int dm_compile_clips(dm_handle* h, int32_t n_clips, const dm_raw_clip_t* raw);
+/* read back one compiled clip (float64, HOST, any pointer may be NULL): what MocapDM exposes as dt, data_config,
+ * data_vel, data_body_xpos, data_geom_xpos.  Only valid after dm_compile_clips. */
+int dm_get_compiled_clip(const dm_handle* h, int32_t clip, int32_t* len, double* dt, double* qpos, double* qvel,
+                         double* body_xpos, double* geom_xpos);
 /* read back the packed fp32 rows (host, [total_rows, row_stride]); rows == NULL just returns the count */
 int dm_get_packed_rows(const dm_handle* h, float* rows, int32_t* total_rows);
 
