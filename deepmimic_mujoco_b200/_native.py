@@ -38,6 +38,17 @@ class RawClip(C.Structure):
                 ("frames", C.c_void_p)]
 
 
+class Policy(C.Structure):
+    _fields_ = [("in_dim", C.c_int32), ("h0", C.c_int32), ("h1", C.c_int32), ("out_dim", C.c_int32)] + \
+               [(k, C.c_void_p) for k in ("W0", "b0", "W1", "b1", "W2", "b2")]
+
+
+class PolicyArgs(C.Structure):
+    _fields_ = [("n", C.c_int32), ("normalize", C.c_int32), ("obs", C.c_void_p), ("action", C.c_void_p),
+                ("obs_norm", C.c_void_p), ("reward", C.c_void_p), ("reward_norm", C.c_void_p),
+                ("act_lo", C.c_float), ("act_hi", C.c_float), ("stream", C.c_void_p)]
+
+
 class StepArgs(C.Structure):
     _fields_ = [("n", C.c_int32), ("layout", C.c_int32), ("ld", C.c_int64),
                 ("qpos", C.c_void_p), ("qvel", C.c_void_p), ("action", C.c_void_p), ("contact", C.c_void_p),
@@ -60,7 +71,8 @@ class ResetArgs(C.Structure):
 SYMBOLS = ["dm_abi_version", "dm_create", "dm_destroy", "dm_last_error", "dm_get_dims", "dm_get_model", "dm_fk_tables",
            "dm_upload_clips", "dm_compile_clips", "dm_get_compiled_clip", "dm_get_packed_rows", "dm_step", "dm_reset", "dm_step_host", "dm_reset_host", "dm_host_buffers",
            "dm_stats_zero", "dm_stats_device_ptr", "dm_stats_read", "dm_launch_count", "dm_step_kernel_time",
-           "dm_set_timing", "dm_set_kernel_variant", "dm_set_contact_mode"]
+           "dm_set_timing", "dm_set_kernel_variant", "dm_set_contact_mode", "dm_policy_upload", "dm_policy_set_normalizer",
+           "dm_policy_normalizer_from_stats", "dm_policy_act"]
 
 _lib = None
 
@@ -98,6 +110,10 @@ def lib():
     L.dm_set_timing.argtypes = [C.c_void_p, C.c_int]
     L.dm_set_kernel_variant.argtypes = [C.c_void_p, C.c_int]
     L.dm_set_contact_mode.argtypes = [C.c_void_p, C.c_int]
+    L.dm_policy_upload.argtypes = [C.c_void_p, C.POINTER(Policy)]
+    L.dm_policy_set_normalizer.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_float]
+    L.dm_policy_normalizer_from_stats.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_void_p]
+    L.dm_policy_act.argtypes = [C.c_void_p, C.POINTER(PolicyArgs)]
     _lib = L
     return L
 

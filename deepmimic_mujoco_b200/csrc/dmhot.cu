@@ -13,6 +13,7 @@
 #include "dm_tile_kernel.cuh"
 #include "dm_pack.h"
 #include "dm_clip_compiler.h"
+#include "dm_policy.cuh"
 
 using namespace dm;
 
@@ -38,6 +39,13 @@ struct dm_handle {
   ClipSet cs{};
   // statistics
   double* d_stats = nullptr;
+  // policy (K6)
+  float* d_pol_packed = nullptr;  // weight chunks in consumption order
+  float* d_pol_bias = nullptr;    // [h0 | h1 | PHEADC]
+  float* d_pol_norm = nullptr;    // [mean | inv_std | reward scale]
+  PolicyParams pol{};             // dims and chunk counts of the uploaded network (pointers filled per launch)
+  float pol_clip_obs = 10.0f, pol_clip_r = 10.0f;
+  bool pol_smem_set = false;
   // host-mode staging (the step's area doubles as the caller-visible pinned buffers of dm_host_buffers)
   Stage step_stage, reset_stage;
   cudaStream_t host_stream = nullptr;
@@ -130,6 +138,9 @@ extern "C" int dm_destroy(dm_handle* h) {
   cudaFree(h->d_rows);
   cudaFree(h->d_state_rows);
   cudaFree(h->d_stats);
+  cudaFree(h->d_pol_packed);
+  cudaFree(h->d_pol_bias);
+  cudaFree(h->d_pol_norm);
   for (auto& c : h->compiled) free_compiled_clip(&c);
   for (Stage* st : {&h->step_stage, &h->reset_stage}) {
     cudaFree(st->d_mem);
@@ -769,5 +780,114 @@ extern "C" int dm_set_contact_mode(dm_handle* h, int mode) {
 extern "C" int dm_set_kernel_variant(dm_handle* h, int variant) {
   if (!h || variant < -1 || variant > 1) return fail(h, DM_E_ARG, "dm_set_kernel_variant: variant must be -1, 0 or 1");
   h->variant = variant;
+  return DM_OK;
+}
+
+// ---- policy (K6) -------------------------------------------------------------------------------------------------------
+extern "C" int dm_policy_upload(dm_handle* h, const dm_policy_t* pol) {
+  if (!h || !pol) return fail(h, DM_E_ARG, "dm_policy_upload: NULL argument");
+  if (!pol->W0 || !pol->b0 || !pol->W1 || !pol->b1 || !pol->W2 || !pol->b2) return fail(h, DM_E_ARG, "dm_policy_upload: a weight pointer is NULL");
+  if (pol->in_dim < 1 || pol->in_dim > PMAX_IN || pol->h0 < 1 || pol->h0 > PMAX_H0 || pol->h1 < 1 || pol->h1 > PMAX_H1 ||
+      pol->out_dim < 1 || pol->out_dim > PMAX_OUT)
+    return fail(h, DM_E_ARG, "dm_policy_upload: supported sizes are in <= %d, hidden <= [%d, %d], out <= %d (got %d -> %d -> %d -> %d)",
+                PMAX_IN, PMAX_H0, PMAX_H1, PMAX_OUT, pol->in_dim, pol->h0, pol->h1, pol->out_dim);
+  CU(h, cudaSetDevice(h->device));
+  const int in = pol->in_dim, in_pad = (in + PK - 1) / PK * PK, h0 = pol->h0, h0p = (h0 + 127) / 128 * 128, h1 = pol->h1, h1p = 128,
+            out = pol->out_dim;
+  const int big = (h0p / 128) * (in_pad / PK) + h0p / PK, small = h1p / PK;
+  std::vector<float> packed((size_t)big * PCHUNK + (size_t)small * PK * PHEADC, 0.0f), bias(h0p + h1p + PHEADC, 0.0f);
+  float* w = packed.data();
+  for (int n0 = 0; n0 < h0p; n0 += 128)        // layer 0, one 128-column pass at a time
+    for (int k0 = 0; k0 < in_pad; k0 += PK, w += PCHUNK)
+      for (int kk = 0; kk < PK; ++kk)
+        for (int c = 0; c < 128; ++c)
+          if (k0 + kk < in && n0 + c < h0) w[kk * 128 + c] = pol->W0[(size_t)(k0 + kk) * h0 + n0 + c];
+  for (int k0 = 0; k0 < h0p; k0 += PK, w += PCHUNK)  // layer 1
+    for (int kk = 0; kk < PK; ++kk)
+      for (int c = 0; c < 128; ++c)
+        if (k0 + kk < h0 && c < h1) w[kk * 128 + c] = pol->W1[(size_t)(k0 + kk) * h1 + c];
+  for (int k0 = 0; k0 < h1p; k0 += PK, w += PK * PHEADC)  // head
+    for (int kk = 0; kk < PK; ++kk)
+      for (int c = 0; c < PHEADC; ++c)
+        if (k0 + kk < h1 && c < out) w[kk * PHEADC + c] = pol->W2[(size_t)(k0 + kk) * out + c];
+  for (int i = 0; i < h0; ++i) bias[i] = pol->b0[i];
+  for (int i = 0; i < h1; ++i) bias[h0p + i] = pol->b1[i];
+  for (int i = 0; i < out; ++i) bias[h0p + h1p + i] = pol->b2[i];
+  cudaFree(h->d_pol_packed);
+  cudaFree(h->d_pol_bias);
+  h->d_pol_packed = h->d_pol_bias = nullptr;
+  CU(h, cudaMalloc(&h->d_pol_packed, packed.size() * sizeof(float)));
+  CU(h, cudaMalloc(&h->d_pol_bias, bias.size() * sizeof(float)));
+  CU(h, cudaMemcpy(h->d_pol_packed, packed.data(), packed.size() * sizeof(float), cudaMemcpyHostToDevice));
+  CU(h, cudaMemcpy(h->d_pol_bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
+  if (!h->d_pol_norm) {
+    std::vector<float> id(2 * PMAX_IN + 1, 0.0f);
+    for (int i = PMAX_IN; i <= 2 * PMAX_IN; ++i) id[i] = 1.0f;
+    CU(h, cudaMalloc(&h->d_pol_norm, id.size() * sizeof(float)));
+    CU(h, cudaMemcpy(h->d_pol_norm, id.data(), id.size() * sizeof(float), cudaMemcpyHostToDevice));
+  }
+  PolicyParams& q = h->pol;
+  q = PolicyParams{};
+  q.in = in; q.in_pad = in_pad; q.h0 = h0p; q.h1 = h1p; q.out = out;
+  q.big_chunks = big; q.chunks_per_tile = big + small;
+  return DM_OK;
+}
+
+extern "C" int dm_policy_set_normalizer(dm_handle* h, int32_t dim, const float* mean, const float* var, float eps, float clip_obs,
+                                        float ret_var, float clip_reward) {
+  if (!h) return fail(h, DM_E_ARG, "dm_policy_set_normalizer: NULL handle");
+  if (!h->d_pol_norm) return fail(h, DM_E_STATE, "dm_policy_set_normalizer: no policy uploaded (call dm_policy_upload first)");
+  if (dim < 0 || dim > PMAX_IN || (mean && !var)) return fail(h, DM_E_ARG, "dm_policy_set_normalizer: dim %d, mean / var inconsistent", dim);
+  CU(h, cudaSetDevice(h->device));
+  std::vector<float> v(2 * PMAX_IN + 1, 0.0f);
+  for (int i = 0; i < PMAX_IN; ++i) {
+    v[i] = mean && i < dim ? mean[i] : 0.0f;
+    v[PMAX_IN + i] = mean && i < dim ? (float)(1.0 / sqrt((double)var[i] + (double)eps)) : 1.0f;
+  }
+  v[2 * PMAX_IN] = (float)(1.0 / sqrt((double)ret_var + (double)eps));
+  CU(h, cudaMemcpy(h->d_pol_norm, v.data(), v.size() * sizeof(float), cudaMemcpyHostToDevice));
+  h->pol_clip_obs = clip_obs;
+  h->pol_clip_r = clip_reward;
+  return DM_OK;
+}
+
+extern "C" int dm_policy_normalizer_from_stats(dm_handle* h, float eps, float clip_obs, float clip_reward, void* stream) {
+  if (!h) return fail(h, DM_E_ARG, "dm_policy_normalizer_from_stats: NULL handle");
+  if (!h->d_pol_norm) return fail(h, DM_E_STATE, "dm_policy_normalizer_from_stats: no policy uploaded (call dm_policy_upload first)");
+  if (h->dims.obs_dim > PMAX_IN) return fail(h, DM_E_ARG, "dm_policy_normalizer_from_stats: obs_dim %d > %d", h->dims.obs_dim, PMAX_IN);
+  CU(h, cudaSetDevice(h->device));
+  policy_norm_from_stats_kernel<<<1, PMAX_IN, 0, (cudaStream_t)stream>>>(h->d_stats, h->dims.obs_dim, eps, h->d_pol_norm,
+                                                                        h->d_pol_norm + 2 * PMAX_IN);
+  h->launches++;
+  CU(h, cudaGetLastError());
+  h->pol_clip_obs = clip_obs;
+  h->pol_clip_r = clip_reward;
+  return DM_OK;
+}
+
+extern "C" int dm_policy_act(dm_handle* h, const dm_policy_args* a) {
+  if (!h || !a) return fail(h, DM_E_ARG, "dm_policy_act: NULL argument");
+  if (!h->d_pol_packed) return fail(h, DM_E_STATE, "dm_policy_act: no policy uploaded (call dm_policy_upload first)");
+  if (a->n < 0) return fail(h, DM_E_ARG, "dm_policy_act: n = %d", a->n);
+  if (a->n == 0) return DM_OK;
+  if (!a->obs || !a->action) return fail(h, DM_E_ARG, "dm_policy_act: obs / action is NULL");
+  if ((a->reward_norm != nullptr) != (a->reward != nullptr)) return fail(h, DM_E_ARG, "dm_policy_act: reward and reward_norm go together");
+  CU(h, cudaSetDevice(h->device));
+  if (!h->pol_smem_set) {
+    CU(h, cudaFuncSetAttribute(policy_mlp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPolicySmemBytes));
+    h->pol_smem_set = true;
+  }
+  PolicyParams p = h->pol;
+  p.n = a->n;
+  p.n_tiles = (a->n + PM - 1) / PM;
+  p.obs = a->obs; p.action = a->action; p.obs_norm = a->obs_norm; p.reward = a->reward; p.reward_norm = a->reward_norm;
+  p.packed = h->d_pol_packed; p.bias = h->d_pol_bias; p.norm = h->d_pol_norm;
+  p.clip_obs = h->pol_clip_obs; p.clip_r = h->pol_clip_r; p.act_lo = a->act_lo; p.act_hi = a->act_hi;
+  p.normalize = a->normalize != 0;
+  p.use_tma = (reinterpret_cast<uintptr_t>(a->obs) & 15u) == 0;
+  const int grid = p.n_tiles < h->num_sms ? p.n_tiles : h->num_sms;
+  policy_mlp_kernel<<<grid, 256, kPolicySmemBytes, (cudaStream_t)a->stream>>>(p);
+  h->launches++;
+  CU(h, cudaGetLastError());
   return DM_OK;
 }

@@ -161,6 +161,41 @@ class HotPath:
         N.check(self.L.dm_get_packed_rows(self.h, N.np_ptr(rows), C.byref(n)), self.h, "dm_get_packed_rows")
         return rows
 
+    # ------------------------------------------------------------------ policy (K6)
+    def policy_upload(self, W0, b0, W1, b1, W2, b2):
+        """Two tanh layers + linear head, weights as np.matmul(x, W) + b uses them (extracted_policy.py:471-478)."""
+        arrs = [np.ascontiguousarray(a, dtype=np.float32) for a in (W0, b0, W1, b1, W2, b2)]
+        W0, b0, W1, b1, W2, b2 = arrs
+        assert W0.ndim == 2 and W1.shape[0] == W0.shape[1] and W2.shape[0] == W1.shape[1]
+        assert b0.shape == (W0.shape[1],) and b1.shape == (W1.shape[1],) and b2.shape == (W2.shape[1],)
+        pol = N.Policy(W0.shape[0], W0.shape[1], W1.shape[1], W2.shape[1], *[N.np_ptr(a) for a in arrs])
+        N.check(self.L.dm_policy_upload(self.h, C.byref(pol)), self.h, "dm_policy_upload")
+        self.policy_dims = (W0.shape[0], W0.shape[1], W1.shape[1], W2.shape[1])
+
+    def policy_set_normalizer(self, mean=None, var=None, eps=1e-8, clip_obs=10.0, ret_var=1.0, clip_reward=10.0):
+        m = None if mean is None else np.ascontiguousarray(mean, dtype=np.float32)
+        v = None if var is None else np.ascontiguousarray(var, dtype=np.float32)
+        N.check(self.L.dm_policy_set_normalizer(self.h, 0 if m is None else len(m), N.np_ptr(m), N.np_ptr(v), eps, clip_obs,
+                                                ret_var, clip_reward), self.h, "dm_policy_set_normalizer")
+
+    def policy_normalizer_from_stats(self, eps=1e-8, clip_obs=10.0, clip_reward=10.0, stream=None):
+        """mean / variance from the statistics the step kernels accumulated (all-reduce them first on several GPUs)."""
+        if stream is None:
+            import torch
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        N.check(self.L.dm_policy_normalizer_from_stats(self.h, eps, clip_obs, clip_reward, stream), self.h,
+                "dm_policy_normalizer_from_stats")
+
+    def policy_act(self, n, obs, action, normalize=False, obs_norm=None, reward=None, reward_norm=None,
+                   act_lo=-np.inf, act_hi=np.inf, stream=None):
+        """Device buffers (torch CUDA tensors); asynchronous on `stream` (default: torch's current stream)."""
+        if stream is None:
+            import torch
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        a = N.PolicyArgs(int(n), 1 if normalize else 0, self._ptr(obs), self._ptr(action), self._ptr(obs_norm),
+                         self._ptr(reward), self._ptr(reward_norm), float(act_lo), float(act_hi), stream)
+        N.check(self.L.dm_policy_act(self.h, C.byref(a)), self.h, "dm_policy_act")
+
     # ------------------------------------------------------------------ step / reset
     @staticmethod
     def _ptr(x):

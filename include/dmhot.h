@@ -208,6 +208,34 @@ int dm_set_contact_mode(dm_handle* h, int mode);
 /* 0 = generic strided kernel, 1 = shared-memory tile kernel with TMA bulk copies (AoS only); default auto */
 int dm_set_kernel_variant(dm_handle* h, int variant);
 
+/* ---- policy inference on the device -------------------------------------------------------------
+ * The reference's ExtractedPolicy.act (src/extracted_policy.py:471-478): two tanh layers and a linear head, the
+ * architecture sb3_ppo.py trains (net_arch [256, 128], src/sb3_ppo.py:265), preceded by the observation normaliser
+ * clip((obs - mean) / sqrt(var + eps), +-clip_obs) fed from this library's running statistics.  One fused kernel;
+ * the observations the step wrote never leave the GPU between environment and policy. */
+typedef struct {
+  int32_t in_dim, h0, h1, out_dim;     /* in_dim <= 128, h0 <= 256, h1 <= 128, out_dim <= 32 */
+  const float *W0, *b0, *W1, *b1, *W2, *b2; /* HOST; W row-major [fan_in, fan_out]: np.matmul(x, W) + b */
+} dm_policy_t;
+typedef struct {
+  int32_t n;
+  int32_t normalize;      /* != 0: apply the observation normaliser before the first layer */
+  const float* obs;       /* DEVICE [n, in_dim] */
+  float* action;          /* DEVICE [n, out_dim]: the action mean (deterministic policy) */
+  float* obs_norm;        /* DEVICE [n, in_dim] or NULL: the normalised observations (for a learner) */
+  const float* reward;    /* DEVICE [n] or NULL */
+  float* reward_norm;     /* DEVICE [n] or NULL: clip(reward * reward_scale, +-clip_reward) */
+  float act_lo, act_hi;   /* clip of the action mean (SB3 predict() clips to the Box); -INF / +INF for none */
+  void* stream;
+} dm_policy_args;
+int dm_policy_upload(dm_handle* h, const dm_policy_t* policy);
+/* mean / var HOST [dim]; NULL mean = identity.  reward scale = 1 / sqrt(ret_var + eps). */
+int dm_policy_set_normalizer(dm_handle* h, int32_t dim, const float* mean, const float* var, float eps, float clip_obs,
+                             float ret_var, float clip_reward);
+/* same, computed on the device from the statistics accumulators (dm_stats_*; population variance) */
+int dm_policy_normalizer_from_stats(dm_handle* h, float eps, float clip_obs, float clip_reward, void* stream);
+int dm_policy_act(dm_handle* h, const dm_policy_args* a);
+
 #ifdef __cplusplus
 }
 #endif
