@@ -172,6 +172,10 @@ class HotPath:
         N.check(self.L.dm_policy_upload(self.h, C.byref(pol)), self.h, "dm_policy_upload")
         self.policy_dims = (W0.shape[0], W0.shape[1], W1.shape[1], W2.shape[1])
 
+    def set_policy_variant(self, variant):
+        """0 = fp32 CUDA-core kernel, 1 = tcgen05 tensor-core kernel (default)."""
+        N.check(self.L.dm_set_policy_variant(self.h, int(variant)), self.h, "dm_set_policy_variant")
+
     def policy_set_normalizer(self, mean=None, var=None, eps=1e-8, clip_obs=10.0, ret_var=1.0, clip_reward=10.0):
         m = None if mean is None else np.ascontiguousarray(mean, dtype=np.float32)
         v = None if var is None else np.ascontiguousarray(var, dtype=np.float32)

@@ -235,6 +235,9 @@ int dm_policy_set_normalizer(dm_handle* h, int32_t dim, const float* mean, const
 /* same, computed on the device from the statistics accumulators (dm_stats_*; population variance) */
 int dm_policy_normalizer_from_stats(dm_handle* h, float eps, float clip_obs, float clip_reward, void* stream);
 int dm_policy_act(dm_handle* h, const dm_policy_args* a);
+/* 0 = fp32 on the CUDA cores, 1 = tcgen05 tensor cores with every fp32 operand split into two fp16 halves and three
+ * MMAs per product (fp32-level accuracy); default 1 */
+int dm_set_policy_variant(dm_handle* h, int variant);
 
 #ifdef __cplusplus
 }

@@ -21,10 +21,15 @@ def _close(got, want, rel=1e-5, floor=1.0):
     assert np.all(err <= tol), "max err %.3e (tol %.3e) at %s" % (err.max(), tol.flat[err.argmax()], np.unravel_index(err.argmax(), err.shape))
 
 
-def test_reference_known_answer_and_seeded_outputs():
+VARIANTS = [0, 1]  # 0 = fp32 CUDA cores (K6a), 1 = tcgen05 tensor cores with fp16 hi/lo operand splitting (K6b)
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_reference_known_answer_and_seeded_outputs(variant):
     from deepmimic_mujoco_b200.policy import ExtractedPolicy
     z = np.load(GOLD)
     pol = ExtractedPolicy.from_npz(GOLD)
+    pol.hp.set_policy_variant(variant)
     assert (pol.obs_shape, pol.act_shape) == (66, 28)
     _close(pol.act(z["kat_obs"]), z["kat_expected"])
     assert np.allclose(pol.act(z["kat_obs"]), z["kat_expected"], rtol=1e-5, atol=1e-6)  # the reference's own criterion
@@ -32,9 +37,10 @@ def test_reference_known_answer_and_seeded_outputs():
     pol.close()
 
 
+@pytest.mark.parametrize("variant", VARIANTS)
 @pytest.mark.parametrize("dims,n", [((67, 256, 128, 28), 128 * 5 + 37), ((85, 256, 128, 23), 300), ((98, 200, 96, 23), 1000),
                                     ((3, 16, 8, 1), 129), ((128, 256, 128, 32), 128 * 150)])
-def test_other_shapes_match_oracle(dims, n):
+def test_other_shapes_match_oracle(dims, n, variant):
     import torch
     from deepmimic_mujoco_b200.hotpath import HotPath
     from oracle.policy import mlp_act
@@ -43,6 +49,7 @@ def test_other_shapes_match_oracle(dims, n):
     W = [rng.normal(0, 1.0 / np.sqrt(a), (a, b)).astype(np.float32) for a, b in ((i, h0), (h0, h1), (h1, o))]
     B = [rng.normal(0, 0.2, b).astype(np.float32) for b in (h0, h1, o)]
     hp = HotPath("humanoid3d")
+    hp.set_policy_variant(variant)
     hp.policy_upload(W[0], B[0], W[1], B[1], W[2], B[2])
     obs = rng.normal(0, 1.5, (n, i)).astype(np.float32)
     want = mlp_act(obs.astype(np.float64), *[x.astype(np.float64) for x in (W[0], B[0], W[1], B[1], W[2], B[2])])
@@ -56,7 +63,8 @@ def test_other_shapes_match_oracle(dims, n):
     hp.close()
 
 
-def test_normaliser_reward_scaling_and_action_clip():
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_normaliser_reward_scaling_and_action_clip(variant):
     import torch
     from deepmimic_mujoco_b200.hotpath import HotPath
     from oracle import policy as OP
@@ -69,6 +77,7 @@ def test_normaliser_reward_scaling_and_action_clip():
     rew = rng.normal(0.5, 0.3, n).astype(np.float32)
     mean, var = obs.mean(0).astype(np.float32), obs.var(0).astype(np.float32)
     hp = HotPath("humanoid3d")
+    hp.set_policy_variant(variant)
     hp.policy_upload(*W)
     hp.policy_set_normalizer(mean, var, eps=1e-8, clip_obs=5.0, ret_var=0.09, clip_reward=2.0)
     d = torch.device("cuda")
