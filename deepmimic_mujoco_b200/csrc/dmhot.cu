@@ -43,7 +43,6 @@ struct dm_handle {
   // policy (K6)
   float* d_pol_packed = nullptr;  // weight chunks in consumption order
   uint8_t* d_pol_packed16 = nullptr;  // the same stream as fp16 hi / lo pairs for the tensor-core kernel
-  int pol_big16 = 0, pol_chunks16 = 0;
   int pol_variant = 1;            // 0 = fp32 CUDA cores (K6a), 1 = tcgen05 (K6b)
   bool pol_tc_smem_set = false;
   float* d_pol_bias = nullptr;    // [h0 | h1 | PHEADC]
@@ -817,18 +816,18 @@ extern "C" int dm_policy_upload(dm_handle* h, const dm_policy_t* pol) {
     for (int kk = 0; kk < PK; ++kk)
       for (int c = 0; c < PHEADC; ++c)
         if (k0 + kk < h1 && c < out) w[kk * PHEADC + c] = pol->W2[(size_t)(k0 + kk) * out + c];
-  // the same stream for the tensor-core kernel: per k-step of 16 [B_hi | B_lo], each [2 k-chunks][N][8] fp16
-  // (K-major core matrices, see dm_policy_tc.cuh), layer 0 / layer 1 as 128-wide halves
-  const int halves = h0p / 128, big16 = halves * (in_pad / 16) + halves * 8, small16 = 8;
-  std::vector<__half> p16((size_t)big16 * 4096 + (size_t)small16 * 1024, __float2half_rn(0.0f));
+  // the weights for the tensor-core kernel: layer 0 | layer 1 | head; per k-step of 16 [B_hi | B_lo], each
+  // [2 k-chunks][N][8] fp16 (K-major core matrices, see dm_policy_tc.cuh) with N = h0p, 128, PHEADC
+  std::vector<__half> p16((size_t)(in_pad / 16) * h0p * 32 * 2 + (size_t)(h0p / 16) * 128 * 32 * 2 + (size_t)8 * PHEADC * 32 * 2,
+                          __float2half_rn(0.0f));
   {
     __half* o = p16.data();
-    auto emit = [&](int n_cols, auto&& weight /* (k, n) -> float, 0 outside */, int k0, int n0) {
+    auto emit = [&](int n_cols, auto&& weight /* (k, n) -> float, 0 outside */, int k0) {
       for (int part = 0; part < 2; ++part)  // hi, lo
         for (int kc = 0; kc < 2; ++kc)
           for (int n = 0; n < n_cols; ++n)
             for (int k8 = 0; k8 < 8; ++k8) {
-              const float x = weight(k0 + kc * 8 + k8, n0 + n);
+              const float x = weight(k0 + kc * 8 + k8, n);
               const __half hi = __float2half_rn(x);
               *o++ = part == 0 ? hi : __float2half_rn(x - __half2float(hi));
             }
@@ -836,11 +835,9 @@ extern "C" int dm_policy_upload(dm_handle* h, const dm_policy_t* pol) {
     auto w0 = [&](int k, int n) { return k < in && n < h0 ? pol->W0[(size_t)k * h0 + n] : 0.0f; };
     auto w1 = [&](int k, int n) { return k < h0 && n < h1 ? pol->W1[(size_t)k * h1 + n] : 0.0f; };
     auto w2 = [&](int k, int n) { return k < h1 && n < out ? pol->W2[(size_t)k * out + n] : 0.0f; };
-    for (int hf = 0; hf < halves; ++hf)
-      for (int k0 = 0; k0 < in_pad; k0 += 16) emit(128, w0, k0, 128 * hf);
-    for (int hf = 0; hf < halves; ++hf)
-      for (int k0 = 0; k0 < 128; k0 += 16) emit(128, w1, 128 * hf + k0, 0);
-    for (int k0 = 0; k0 < 128; k0 += 16) emit(PHEADC, w2, k0, 0);
+    for (int k0 = 0; k0 < in_pad; k0 += 16) emit(h0p, w0, k0);
+    for (int k0 = 0; k0 < h0p; k0 += 16) emit(128, w1, k0);
+    for (int k0 = 0; k0 < 128; k0 += 16) emit(PHEADC, w2, k0);
   }
   for (int i = 0; i < h0; ++i) bias[i] = pol->b0[i];
   for (int i = 0; i < h1; ++i) bias[h0p + i] = pol->b1[i];
@@ -852,8 +849,6 @@ extern "C" int dm_policy_upload(dm_handle* h, const dm_policy_t* pol) {
   h->d_pol_packed16 = nullptr;
   CU(h, cudaMalloc(&h->d_pol_packed16, p16.size() * sizeof(__half)));
   CU(h, cudaMemcpy(h->d_pol_packed16, p16.data(), p16.size() * sizeof(__half), cudaMemcpyHostToDevice));
-  h->pol_big16 = big16;
-  h->pol_chunks16 = big16 + small16;
   CU(h, cudaMalloc(&h->d_pol_packed, packed.size() * sizeof(float)));
   CU(h, cudaMalloc(&h->d_pol_bias, bias.size() * sizeof(float)));
   CU(h, cudaMemcpy(h->d_pol_packed, packed.data(), packed.size() * sizeof(float), cudaMemcpyHostToDevice));
@@ -936,9 +931,7 @@ extern "C" int dm_policy_act(dm_handle* h, const dm_policy_args* a) {
       h->pol_tc_smem_set = true;
     }
     PolicyTcParams q{p, h->d_pol_packed16};
-    q.p.big_chunks = h->pol_big16;
-    q.p.chunks_per_tile = h->pol_chunks16;
-    policy_mlp_tc_kernel<<<grid, 192, kPolicyTcSmemBytes, (cudaStream_t)a->stream>>>(q);
+    policy_mlp_tc_kernel<<<grid, TC_THREADS, kPolicyTcSmemBytes, (cudaStream_t)a->stream>>>(q);
     h->launches++;
     CU(h, cudaGetLastError());
     return DM_OK;

@@ -24,7 +24,8 @@ def main():
     hp.policy_set_normalizer(np.zeros(67), np.ones(67))
     dev = torch.device("cuda", 0)
     fma_per_env = dims[0] * dims[1] + dims[1] * dims[2] + dims[2] * dims[3]
-    for n in sizes:
+    for variant, n in [(v, n) for v in (0, 1) for n in sizes]:
+        hp.set_policy_variant(variant)
         obs = torch.randn(n, dims[0], device=dev)
         act = torch.empty(n, dims[3], device=dev)
         for _ in range(5):
@@ -43,7 +44,7 @@ def main():
         mhz = float(clk or 1965)
         peak = 148 * 128 * mhz * 1e6
         fma = fma_per_env * n / (ms * 1e-3)
-        print(json.dumps({"kernel": "policy_mlp_kernel", "envs": n, "ms": ms, "env_per_s": n / (ms * 1e-3), "fma_per_env": fma_per_env,
+        print(json.dumps({"kernel": "policy_mlp_tc_kernel" if variant else "policy_mlp_kernel", "envs": n, "ms": ms, "env_per_s": n / (ms * 1e-3), "fma_per_env": fma_per_env,
                           "TFLOPs": 2 * fma / 1e12, "fp32_peak_TFLOPs": 2 * peak / 1e12, "frac": fma / peak, "sm_mhz": mhz}))
 
 
