@@ -45,6 +45,8 @@ struct dm_handle {
   uint8_t* d_pol_packed16 = nullptr;  // the same stream as fp16 hi / lo pairs for the tensor-core kernel
   int pol_variant = 1;            // 0 = fp32 CUDA cores (K6a), 1 = tcgen05 (K6b)
   bool pol_tc_smem_set = false;
+  int pol_trace_cta = 0;
+  long long* pol_trace = nullptr;  // debug: device buffer [64][8] of clock64 marks (dm_policy_set_trace)
   float* d_pol_bias = nullptr;    // [h0 | h1 | PHEADC]
   float* d_pol_norm = nullptr;    // [mean | inv_std | reward scale]
   PolicyParams pol{};             // dims and chunk counts of the uploaded network (pointers filled per launch)
@@ -816,18 +818,17 @@ extern "C" int dm_policy_upload(dm_handle* h, const dm_policy_t* pol) {
     for (int kk = 0; kk < PK; ++kk)
       for (int c = 0; c < PHEADC; ++c)
         if (k0 + kk < h1 && c < out) w[kk * PHEADC + c] = pol->W2[(size_t)(k0 + kk) * out + c];
-  // the weights for the tensor-core kernel: layer 0 | layer 1 | head; per k-step of 16 [B_hi | B_lo], each
-  // [2 k-chunks][N][8] fp16 (K-major core matrices, see dm_policy_tc.cuh) with N = h0p, 128, PHEADC
-  std::vector<__half> p16((size_t)(in_pad / 16) * h0p * 32 * 2 + (size_t)(h0p / 16) * 128 * 32 * 2 + (size_t)8 * PHEADC * 32 * 2,
-                          __float2half_rn(0.0f));
+  // the weights for the tensor-core kernel: layer 0 (one 128-column half after the other) | layer 1 | head; per k-step of
+  // 16 [B_hi | B_lo], each [2 k-chunks][N][8] fp16 (K-major core matrices, see dm_policy_tc.cuh), N = 128 (head: PHEADC)
+  std::vector<__half> p16((size_t)((h0p / 128) * (in_pad / 16) + h0p / 16) * 4096 + (size_t)8 * PHEADC * 32, __float2half_rn(0.0f));
   {
     __half* o = p16.data();
-    auto emit = [&](int n_cols, auto&& weight /* (k, n) -> float, 0 outside */, int k0) {
+    auto emit = [&](int n_cols, auto&& weight /* (k, n) -> float, 0 outside */, int k0, int n0) {
       for (int part = 0; part < 2; ++part)  // hi, lo
         for (int kc = 0; kc < 2; ++kc)
           for (int n = 0; n < n_cols; ++n)
             for (int k8 = 0; k8 < 8; ++k8) {
-              const float x = weight(k0 + kc * 8 + k8, n);
+              const float x = weight(k0 + kc * 8 + k8, n0 + n);
               const __half hi = __float2half_rn(x);
               *o++ = part == 0 ? hi : __float2half_rn(x - __half2float(hi));
             }
@@ -835,9 +836,10 @@ extern "C" int dm_policy_upload(dm_handle* h, const dm_policy_t* pol) {
     auto w0 = [&](int k, int n) { return k < in && n < h0 ? pol->W0[(size_t)k * h0 + n] : 0.0f; };
     auto w1 = [&](int k, int n) { return k < h0 && n < h1 ? pol->W1[(size_t)k * h1 + n] : 0.0f; };
     auto w2 = [&](int k, int n) { return k < h1 && n < out ? pol->W2[(size_t)k * out + n] : 0.0f; };
-    for (int k0 = 0; k0 < in_pad; k0 += 16) emit(h0p, w0, k0);
-    for (int k0 = 0; k0 < h0p; k0 += 16) emit(128, w1, k0);
-    for (int k0 = 0; k0 < 128; k0 += 16) emit(PHEADC, w2, k0);
+    for (int hf = 0; hf < h0p / 128; ++hf)
+      for (int k0 = 0; k0 < in_pad; k0 += 16) emit(128, w0, k0, 128 * hf);
+    for (int k0 = 0; k0 < h0p; k0 += 16) emit(128, w1, k0, 0);
+    for (int k0 = 0; k0 < 128; k0 += 16) emit(PHEADC, w2, k0, 0);
   }
   for (int i = 0; i < h0; ++i) bias[i] = pol->b0[i];
   for (int i = 0; i < h1; ++i) bias[h0p + i] = pol->b1[i];
@@ -898,6 +900,14 @@ extern "C" int dm_policy_normalizer_from_stats(dm_handle* h, float eps, float cl
   return DM_OK;
 }
 
+// debug hook for tools/policy_trace.py (not part of the public header): per-tile event clocks of CTA 0
+extern "C" int dm_policy_set_trace(dm_handle* h, long long* device_buffer, int cta) {
+  if (!h) return DM_E_ARG;
+  h->pol_trace = device_buffer;
+  h->pol_trace_cta = cta;
+  return DM_OK;
+}
+
 extern "C" int dm_set_policy_variant(dm_handle* h, int variant) {
   if (!h || variant < 0 || variant > 1) return fail(h, DM_E_ARG, "dm_set_policy_variant: variant must be 0 (fp32 CUDA cores) or 1 (tensor cores)");
   h->pol_variant = variant;
@@ -927,11 +937,11 @@ extern "C" int dm_policy_act(dm_handle* h, const dm_policy_args* a) {
   const int grid = p.n_tiles < h->num_sms ? p.n_tiles : h->num_sms;
   if (h->pol_variant == 1) {
     if (!h->pol_tc_smem_set) {
-      CU(h, cudaFuncSetAttribute(policy_mlp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPolicyTcSmemBytes));
+      CU(h, cudaFuncSetAttribute(policy_mlp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
       h->pol_tc_smem_set = true;
     }
-    PolicyTcParams q{p, h->d_pol_packed16};
-    policy_mlp_tc_kernel<<<grid, TC_THREADS, kPolicyTcSmemBytes, (cudaStream_t)a->stream>>>(q);
+    PolicyTcParams q{p, h->d_pol_packed16, policy_tc_stages(p.in), policy_tc_raw_bytes(p.in), h->pol_trace, h->pol_trace_cta};
+    policy_mlp_tc_kernel<<<grid, TC_THREADS, policy_tc_smem_bytes(p.in), (cudaStream_t)a->stream>>>(q);
     h->launches++;
     CU(h, cudaGetLastError());
     return DM_OK;
