@@ -252,6 +252,15 @@ class DPVecEnv:
                              qpos=t(self.qpos), qvel=t(self.qvel))
         return self._dev
 
+    def reset_tensors(self):
+        """Resident reset of every environment (device RNG reference-state init); returns the device observation
+        tensor.  The reference states are in device_buffers()['qpos'] / ['qvel']."""
+        b = self.device_buffers()
+        self._counter += 1
+        self.hp.reset(self.num_envs, b["idx"], b["ep_len"], b["clip"], b["obs"], mask=None, qpos=b["qpos"], qvel=b["qvel"],
+                      ep_return=b["ep_return"], seed=self._seed, counter=self._counter)
+        return b["obs"]
+
     def step_tensors(self, actions, qpos, qvel, contact=None, auto_reset=True, stats=False):
         """Resident path: everything stays on the GPU; returns (obs, reward, done) tensors owned by the env.
         With auto_reset, done envs are re-initialised by a masked reset launch (their previous observation goes to

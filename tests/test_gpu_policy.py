@@ -143,3 +143,26 @@ def test_policy_argument_errors():
     with pytest.raises(N.DmError, match="go together"):
         hp.policy_act(4, x, a, reward=torch.zeros(4, device="cuda"))
     hp.close()
+
+
+def test_policy_in_the_resident_loop():
+    """DPVecEnv.step_tensors -> ExtractedPolicy.act_device on the env's own device buffers and handle, against the
+    oracle MLP on the observations the env produced."""
+    import torch
+    from deepmimic_mujoco_b200.policy import ExtractedPolicy
+    from deepmimic_mujoco_b200.vec_env import DPVecEnv
+    from oracle.policy import mlp_act
+    n = 128 * 4 + 9
+    env = DPVecEnv(n, motion="walk", robot="humanoid3d", seed=3)
+    rng = np.random.default_rng(1)
+    W = [rng.normal(0, 0.1, sh).astype(np.float32) for sh in ((67, 256), (256,), (256, 128), (128,), (128, 28), (28,))]
+    pol = ExtractedPolicy(*W, hotpath=env.hp)
+    obs = env.reset_tensors()
+    b = env.device_buffers()
+    for _ in range(3):
+        act = pol.act_device(obs, act_lo=-2.0, act_hi=2.0)
+        want = np.clip(mlp_act(obs.cpu().numpy().astype(np.float64), *[w.astype(np.float64) for w in W]), -2.0, 2.0)
+        _close(act.cpu().numpy(), want)
+        obs, rew, done = env.step_tensors(act, b["qpos"], b["qvel"])  # kinematic replay of the reference states
+        assert torch.isfinite(obs).all() and torch.isfinite(rew).all()
+    env.close()
