@@ -238,6 +238,8 @@ def timed_region(wl, steps, warmup, world, allreduce_every, stats_t):
                 dmdist.allreduce_(stats_t)
 
     run(warmup)
+    if world > 1 and stats_t is not None:  # the collective is part of the warm-up too (NCCL connects lazily on first use)
+        dmdist.allreduce_(stats_t)
     wl.restore()
     if stats_t is not None:
         wl.hp.stats_zero(torch.cuda.current_stream().cuda_stream)
