@@ -41,7 +41,8 @@ def _struct_fields(name):
 
 
 @pytest.mark.parametrize("cname,pyname", [("dm_step_args", "StepArgs"), ("dm_reset_args", "ResetArgs"), ("dm_clip_t", "Clip"),
-                                          ("dm_dims_t", "Dims")])
+                                          ("dm_dims_t", "Dims"), ("dm_raw_clip_t", "RawClip"), ("dm_policy_t", "Policy"),
+                                          ("dm_policy_args", "PolicyArgs")])
 def test_ctypes_structs_follow_the_header(cname, pyname):
     from deepmimic_mujoco_b200 import _native
     assert [f[0] for f in getattr(_native, pyname)._fields_] == _struct_fields(cname)
@@ -74,3 +75,28 @@ def test_product_does_not_import_the_oracle():
                 with open(os.path.join(root, f)) as fh:
                     src = fh.read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f
+
+
+def test_ctypes_struct_sizes_match_a_c_compiler(tmp_path):
+    """sizeof / offsetof of every argument block as gcc lays them out == ctypes' layout (padding included)."""
+    import subprocess
+    from deepmimic_mujoco_b200 import _native
+    pairs = [("dm_step_args", "StepArgs"), ("dm_reset_args", "ResetArgs"), ("dm_clip_t", "Clip"), ("dm_dims_t", "Dims"),
+             ("dm_raw_clip_t", "RawClip"), ("dm_policy_t", "Policy"), ("dm_policy_args", "PolicyArgs")]
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "dmhot.h"', 'int main(void) {']
+    for cname, pyname in pairs:
+        lines.append('printf("%s %%zu", sizeof(%s));' % (cname, cname))
+        for f, _ in getattr(_native, pyname)._fields_:
+            lines.append('printf(" %%zu", offsetof(%s, %s));' % (cname, f))
+        lines.append('printf("\\n");')
+    lines += ["return 0;", "}"]
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.check_call(["gcc", "-I", os.path.join(REPO, "include"), "-o", str(exe), str(src)])
+    out = subprocess.check_output([str(exe)], text=True).strip().splitlines()
+    for (cname, pyname), line in zip(pairs, out):
+        nums = [int(x) for x in line.split()[1:]]
+        cls = getattr(_native, pyname)
+        assert nums[0] == C.sizeof(cls), cname
+        assert nums[1:] == [getattr(cls, f).offset for f, _ in cls._fields_], cname
