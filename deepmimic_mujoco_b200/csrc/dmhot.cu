@@ -5,13 +5,16 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/dmhot.h"
 #include "dm_kernels.cuh"
 #include "dm_tile_kernel.cuh"
 #include "dm_pack.h"
+#include "dm_copy_pool.h"
 #include "dm_clip_compiler.h"
 #include "dm_policy.cuh"
 #include "dm_policy_tc.cuh"
@@ -56,6 +59,8 @@ struct dm_handle {
   Stage step_stage, reset_stage;
   cudaStream_t host_stream = nullptr;
   cudaEvent_t obs_event = nullptr;
+  std::unique_ptr<CopyPool> pool;  // helper threads for the staging copies of big host batches (created on first use)
+  int copy_threads = -1;           // -1 = auto (3 helpers when the machine has the cores), DM_COPY_THREADS overrides
   // bookkeeping
   long long launches = 0;
   int variant = -1;  // -1 auto
@@ -119,6 +124,7 @@ extern "C" int dm_create(int device, int robot, int env_kind, dm_handle** out) {
   if (const char* e = getenv("DM_NBUF")) h->nbuf_override = atoi(e);
   if (const char* e = getenv("DM_MAX_GROUPS")) h->max_groups_override = atoi(e);
   if (const char* e = getenv("DM_POLICY_VARIANT")) h->pol_variant = atoi(e) ? 1 : 0;
+  if (const char* e = getenv("DM_COPY_THREADS")) h->copy_threads = atoi(e);
   dispatch(h, [&](auto rb, auto kind) -> int {
     using Rb = decltype(rb);
     using OL = ObsLayout<decltype(kind)::value, Rb>;
@@ -616,8 +622,18 @@ extern "C" int dm_step_host(dm_handle* h, const dm_step_args* a, int64_t* h2d_by
   const StepStage g = carve_step(h, n);
   cudaStream_t s = h->host_stream;
   // a buffer that already IS its staging slot (dm_host_buffers) needs no copy
-  auto in = [](void* slot, const void* src, size_t bytes) { if (src != slot) { if (src) memcpy(slot, src, bytes); else memset(slot, 0, bytes); } };
-  auto out = [](void* dst, const void* slot, size_t bytes) { if (dst && dst != slot) memcpy(dst, slot, bytes); };
+  if (!h->pool) {
+    int helpers = h->copy_threads;
+    if (helpers < 0) {
+      const unsigned hw = std::thread::hardware_concurrency();
+      helpers = hw >= 8 ? 3 : hw >= 4 ? 1 : 0;
+    }
+    if (sizeof(float) * n * d.nq < 192 * 1024) helpers = 0;  // small batches never reach the parallel threshold
+    h->pool.reset(new CopyPool(helpers > 8 ? 8 : helpers));
+  }
+  CopyPool* pool = h->pool.get();
+  auto in = [pool](void* slot, const void* src, size_t bytes) { if (src != slot) { if (src) pool->copy(slot, src, bytes); else memset(slot, 0, bytes); } };
+  auto out = [pool](void* dst, const void* slot, size_t bytes) { if (dst && dst != slot) pool->copy(dst, slot, bytes); };
   // Inputs that are not already in their staging slot are copied there one array at a time, each followed at once
   // by its own H2D transfer, so the DMA of one array overlaps the host memcpy of the next; when every input is in
   // place (dm_host_buffers) the whole input block goes in ONE transfer.
@@ -666,7 +682,7 @@ extern "C" int dm_step_host(dm_handle* h, const dm_step_args* a, int64_t* h2d_by
     CU(h, cudaEventRecord(h->obs_event, s));
     CU(h, cudaMemcpyAsync(hb2 + obs_end, db2 + obs_end, g.end - obs_end, cudaMemcpyDeviceToHost, s));
     CU(h, cudaEventSynchronize(h->obs_event));
-    memcpy(a->obs, g.ho, sizeof(float) * n * d.obs_dim);
+    pool->copy(a->obs, g.ho, sizeof(float) * n * d.obs_dim);
     CU(h, cudaStreamSynchronize(s));
   }
   out(a->reward, g.hr, 4 * n);

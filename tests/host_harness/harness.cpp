@@ -93,3 +93,21 @@ extern "C" int hh_fk_tables(int robot, int n, const double* qpos, const double* 
   if (robot == 0) fkt<Robot_humanoid3d>(n, qpos, qvel, bx, gx); else fkt<Robot_unitree_g1>(n, qpos, qvel, bx, gx);
   return 0;
 }
+
+// ---- CopyPool self-test (csrc/dm_copy_pool.h): parallel copies of random sizes == memcpy ----
+#include "../../deepmimic_mujoco_b200/csrc/dm_copy_pool.h"
+extern "C" int hh_copy_pool_selftest(int helpers, int iters, unsigned seed) {
+  dm::CopyPool pool(helpers);
+  std::vector<unsigned char> src(5u << 20), dst(5u << 20), ref(5u << 20);
+  unsigned x = seed * 2654435761u + 1u;
+  auto rnd = [&] { x ^= x << 13; x ^= x >> 17; x ^= x << 5; return x; };
+  for (auto& b : src) b = (unsigned char)rnd();
+  for (int it = 0; it < iters; ++it) {
+    const size_t bytes = 1 + rnd() % (it % 3 == 0 ? 4000000u : 300000u), off = rnd() % 4096;
+    for (size_t i = 0; i < bytes + 64; ++i) dst[off + i] = ref[off + i] = (unsigned char)(it + i);
+    pool.copy(dst.data() + off, src.data() + (it % 7), bytes);
+    memcpy(ref.data() + off, src.data() + (it % 7), bytes);
+    if (memcmp(dst.data() + off, ref.data() + off, bytes + 64) != 0) return it + 1;  // payload and the bytes behind it
+  }
+  return 0;
+}

@@ -1,6 +1,8 @@
 """The kernel's per-environment arithmetic (csrc/dm_step.cuh + generated FK), compiled for the CPU by
 tests/host_harness, against the golden vectors recorded from the reference.  This is a CPU-side unit
 test of the SAME source the CUDA kernels compile -- the GPU parity tests proper are test_gpu_*.py."""
+import os
+
 import numpy as np
 import pytest
 
@@ -49,3 +51,12 @@ def test_fk_tables_double_matches_oracle():
     be.L.hh_fk_tables(1, len(q), np_ptr(q), np_ptr(v), np_ptr(bx), np_ptr(gx))
     np.testing.assert_allclose(bx, np.asarray(t.data_body_xpos), rtol=0, atol=1e-13)
     np.testing.assert_allclose(gx, np.asarray(t.data_geom_xpos), rtol=0, atol=1e-13)
+
+
+@pytest.mark.parametrize("helpers", [0, 1, 3])
+def test_copy_pool_matches_memcpy(helpers):
+    """dm_copy_pool.h (the helper threads behind dm_step_host's staging copies): 400 copies of random size and alignment,
+    each compared with memcpy including the bytes behind the payload."""
+    import ctypes as C
+    L = C.CDLL(os.path.join(os.path.dirname(os.path.abspath(__file__)), "host_harness", "libhostharness.so"))
+    assert L.hh_copy_pool_selftest(helpers, 400, 7) == 0
