@@ -314,7 +314,7 @@ def e2e_region(args, steps, warmup, seed):
     out = dict(value=args.envs * steps / dt, unit="env-steps/s", h2d_bytes_per_step=int(env.h2d_bytes),
                d2h_bytes_per_step=int(env.d2h_bytes), ms_per_step=1e3 * dt / steps,
                api="DPVecEnv.step(actions, force_state=(qpos, qvel, contact)) with ordinary (pageable) numpy inputs and fresh "
-                   "caller-owned outputs: dm_step_host copies each input into the handle's pinned block and ships it (memcpy "
+                   "caller-owned outputs: dm_step_host copies each input into the handle's pinned block (the copy shared with 3 helper threads) and ships it (memcpy "
                    "of one array overlapping the H2D of the previous), kernel, D2H, observation copied out while the rest lands")
     env.close()
     return out
