@@ -285,6 +285,35 @@ def kernel_time(wl, steps):
     return e0.elapsed_time(e1) / steps, steps
 
 
+def policy_time(hp, device, n):
+    """The consumer of the observation, reported next to the step: fused normaliser + 256/128 tanh MLP
+    (dm_policy_act) on n resident observations, both kernels, CUDA events on the launch stream.  Not part of `value`."""
+    import torch
+    d = hp.dims
+    rng = np.random.default_rng(5)
+    out_dim = min(int(d.na), 32)
+    W = [rng.normal(0, 0.1, sh).astype(np.float32) for sh in ((d.obs_dim, 256), (256,), (256, 128), (128,), (128, out_dim), (out_dim,))]
+    hp.policy_upload(*W)
+    hp.policy_set_normalizer(np.zeros(d.obs_dim, np.float32), np.ones(d.obs_dim, np.float32))
+    obs, act = torch.randn(n, d.obs_dim, device=device), torch.empty(n, out_dim, device=device)
+    res = {"envs": n, "net": "%d-256-128-%d tanh, normaliser on" % (d.obs_dim, out_dim)}
+    for variant, key in ((1, "tensor_core_ms"), (0, "cuda_core_ms")):
+        hp.set_policy_variant(variant)
+        for _ in range(3):
+            hp.policy_act(n, obs, act, normalize=True)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            hp.policy_act(n, obs, act, normalize=True)
+        e1.record()
+        torch.cuda.synchronize()
+        res[key] = e0.elapsed_time(e1) / 10
+    res["env_per_s"] = n / (res["tensor_core_ms"] * 1e-3)
+    hp.set_policy_variant(1)
+    return res
+
+
 def e2e_region(args, steps, warmup, seed):
     """Same metric through the public API a user calls -- DPVecEnv.step(actions, force_state=(qpos, qvel, contact)) with
     HOST numpy buffers: H2D of the step's inputs, kernel, D2H of obs / reward / done / torque every step."""
@@ -494,6 +523,7 @@ def main():
             del w2
             torch.cuda.empty_cache()
         line["sweep"] = sweep
+        line["policy"] = policy_time(wl.hp, device, 1048576)
     if world > 1:
         import torch.distributed as dist
         dist.barrier()
