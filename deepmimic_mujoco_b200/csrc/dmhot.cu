@@ -292,8 +292,9 @@ extern "C" int dm_compile_clips(dm_handle* h, int32_t n_clips, const dm_raw_clip
     const dm_raw_clip_t& r = raw[c];
     const int n_rows = comp[src[c]].len;
     if (r.fixed_row >= n_rows || (r.fixed_row >= 0 && r.virtual_len <= 0)) { drop(); return fail(h, DM_E_ARG, "dm_compile_clips: clip %d: fixed_row / virtual_len inconsistent", c); }
-    cs.clip[c] = ClipDesc{total, r.fixed_row >= 0 ? r.virtual_len : n_rows, r.flags, r.fixed_row};
-    total += n_rows;
+    // a clip that shares another's tables (MotionTransition) indexes that clip's rows: nothing is stored twice
+    cs.clip[c] = ClipDesc{r.same_as >= 0 ? cs.clip[r.same_as].row0 : total, r.fixed_row >= 0 ? r.virtual_len : n_rows, r.flags, r.fixed_row};
+    if (r.same_as < 0) total += n_rows;
   }
   const size_t stride = h->dims.row_stride, sstride = h->dims.nq + h->dims.nv;
   float *d_rows = nullptr, *d_srows = nullptr;
@@ -302,6 +303,7 @@ extern "C" int dm_compile_clips(dm_handle* h, int32_t n_clips, const dm_raw_clip
     return fail(h, DM_E_NOMEM, "dm_compile_clips: %s", cudaGetErrorString(cudaGetLastError()));
   }
   for (int c = 0; c < n_clips; ++c) {
+    if (raw[c].same_as >= 0) continue;
     const CompiledClip& k = comp[src[c]];
     const char* bad = pack_rows_device(h->robot, k, 0, k.len, cs.clip[c].row0, d_rows, d_srows, &h->launches, h->host_stream);
     if (bad) { cudaFree(d_rows); cudaFree(d_srows); drop(); return fail(h, DM_E_CUDA, "dm_compile_clips: %s", bad); }

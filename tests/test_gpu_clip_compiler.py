@@ -81,7 +81,12 @@ def test_device_packed_rows_equal_host_packed_rows(robot, combined):
     else:
         b.upload_mocaps(a.mocaps, [0, 0], a.clip_names)
     ra, rb = a.packed_rows(), b.packed_rows()
-    assert ra.shape == rb.shape and a.clip_lens == b.clip_lens
+    assert a.clip_lens == b.clip_lens
+    if combined:  # the compiler stores the MotionTransition's pose source once; dm_upload_clips is handed (and keeps) a copy
+        assert len(ra) == 76 + 48 + 353 and len(rb) == len(ra) + 353
+        np.testing.assert_array_equal(rb[len(ra):], rb[76 + 48:76 + 48 + 353])
+        rb = rb[:len(ra)]
+    assert ra.shape == rb.shape
     np.testing.assert_allclose(ra, rb, rtol=2e-7, atol=1e-9)
     assert (ra != rb).mean() < 1e-3
     a.close()
