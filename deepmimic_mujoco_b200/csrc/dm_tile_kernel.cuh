@@ -101,7 +101,13 @@ struct TileCfg {
   // a tile buffer row: the input rows (nq + nv floats), later the observation row plus one statistics column (reward)
   static constexpr int ROW = (Rb::NQ + Rb::NV) > OL::DIM + 1 ? (Rb::NQ + Rb::NV) : OL::DIM + 1;
   static constexpr int NCOLS = OL::DIM + 1, NCOLIT = (NCOLS + 31) / 32;
-  static constexpr int BUF_FLOATS = TE * ROW;
+  // robots whose action rows are not a whole number of 128-bit words / actuators (unitree_g1: 23 actions, 37 motors) get
+  // their action tile staged behind the rows by a third bulk copy; the torque pass then reads shared memory instead of
+  // stalling twice per tile on global loads (ncu: 30 % of the G1 kernel's stall samples sat on that pass)
+  static constexpr bool kVecTorque = Rb::NA == Rb::NU && Rb::NA % 4 == 0;
+  static constexpr int ACT_FLOATS = kVecTorque ? 0 : TE * Rb::NA;
+  static_assert((ACT_FLOATS * 4) % 16 == 0, "bulk copies move multiples of 16 bytes");
+  static constexpr int BUF_FLOATS = TE * ROW + ACT_FLOATS;
   static constexpr size_t BUF_BYTES = sizeof(float) * BUF_FLOATS;              // one ring slot
   static constexpr size_t ACC_BYTES = sizeof(double) * (2 * NCOLIT * TE + 4);  // per group, STATS only
   static constexpr int MAXBUF = 12;                                            // ring slots (mbarriers 0 .. MAXBUF-1, table = MAXBUF)
@@ -174,9 +180,11 @@ __global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_co
     const int slot = j % nbuf;
     const long long f0 = ((long long)blockIdx.x + (long long)j * gridDim.x) * TE;
     float* dst = s_ring + (size_t)slot * TC::BUF_FLOATS;
-    mbar_expect_tx(bars + slot, sizeof(float) * TE * (Rb::NQ + Rb::NV));
+    const bool act = TC::ACT_FLOATS != 0 && p.torque != nullptr;
+    mbar_expect_tx(bars + slot, sizeof(float) * (TE * (Rb::NQ + Rb::NV) + (act ? TC::ACT_FLOATS : 0)));
     tma_load_1d(dst, p.qpos + f0 * Rb::NQ, sizeof(float) * TE * Rb::NQ, bars + slot);
     tma_load_1d(dst + TE * Rb::NQ, p.qvel + f0 * Rb::NV, sizeof(float) * TE * Rb::NV, bars + slot);
+    if (act) tma_load_1d(dst + TE * TC::ROW, p.action + f0 * Rb::NA, sizeof(float) * TC::ACT_FLOATS, bars + slot);
   };
 
   if (tid == 0) {
@@ -217,7 +225,7 @@ __global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_co
   // loaded one tile AHEAD, right after the previous tile's observation store is issued, so their global-load
   // latency hides behind the statistics pass and the barrier instead of stalling every warp of the group.
   // (Running the whole torque pass of the next tile there instead was measured slower: 188 vs 179 us at 1 M envs.)
-  constexpr bool kVecTorque = Rb::NA == Rb::NU && Rb::NA % 4 == 0;
+  constexpr bool kVecTorque = TC::kVecTorque;
   constexpr int K4 = Rb::NA / 4, CH = TE * Rb::NA / 4, PER = kVecTorque ? (CH + TE - 1) / TE : 1;
   float4 av[PER];
   EnvState st_n{0, 0, 0};
@@ -240,7 +248,7 @@ __global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_co
   };
   // action -> torque of tile t: a flat, fully coalesced pass over the [TE, NA] tile (contiguous in the row-major
   // action array)
-  auto torque_tile = [&](int t) {
+  auto torque_tile = [&](int t, const float* s_act) {
     const long long e0 = (long long)t * TE;
     if (p.torque) {
       if (kVecTorque) {  // 128-bit path: chunk c covers actuators 4 (c mod NA/4) .. + 3; av[] was loaded by load_ahead
@@ -268,7 +276,7 @@ __global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_co
         }
       } else {  // scalar flat path: output element o = (row, actuator); hand actuators get zero torque
         constexpr int TOT = TE * Rb::NU, PERS = (TOT + TE - 1) / TE, HALF = (PERS + 1) / 2;
-        const float* arow = p.action + e0 * Rb::NA;
+        const float* arow = s_act;  // the tile's [TE, NA] actions, staged by issue_load
         float* trow = p.torque + e0 * Rb::NU;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
@@ -276,7 +284,7 @@ __global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_co
 #pragma unroll
           for (int m = 0; m < HALF; ++m) {
             const int o = gt + (h * HALF + m) * TE, r = o / Rb::NU, k = o - r * Rb::NU;
-            v[m] = (h * HALF + m < PERS && o < TOT && k < Rb::NA) ? __ldg(arow + r * Rb::NA + k) : 0.0f;
+            v[m] = (h * HALF + m < PERS && o < TOT && k < Rb::NA) ? arow[r * Rb::NA + k] : 0.0f;
           }
 #pragma unroll
           for (int m = 0; m < HALF; ++m) {
@@ -307,13 +315,14 @@ __global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_co
     EnvState st = st_n;
     const uint32_t contact = contact_n;
     const float ep_ret0 = ep_ret_n;
-    torque_tile(tile_of(j));  // while the TMA load is in flight; its action chunks were loaded a tile ahead
+    if (kVecTorque) torque_tile(tile_of(j), nullptr);  // while the TMA load is in flight; its action chunks were loaded a tile ahead
     // ---- per-environment step out of shared memory --------------------------------------------------
     if (!table_ready) {
       mbar_wait(bars + TC::MAXBUF, 0);
       table_ready = true;
     }
     mbar_wait(bars + slot, parity);
+    if (!kVecTorque) torque_tile(tile_of(j), buf + TE * TC::ROW);  // out of the staged action tile; the stores drain under the step
     TileIO<KIND, Rb> io;
     io.qp = s_qp + gt * Rb::NQ;
     io.qv = s_qv + gt * Rb::NV;
