@@ -342,9 +342,24 @@ def e2e_region(args, steps, warmup, seed):
     assert obs.shape == (args.envs, env.hp.obs_dim) and len(infos) == args.envs
     out = dict(value=args.envs * steps / dt, unit="env-steps/s", h2d_bytes_per_step=int(env.h2d_bytes),
                d2h_bytes_per_step=int(env.d2h_bytes), ms_per_step=1e3 * dt / steps,
-               api="DPVecEnv.step(actions, force_state=(qpos, qvel, contact)) with ordinary (pageable) numpy inputs and fresh "
-                   "caller-owned outputs: dm_step_host copies each input into the handle's pinned block (the copy shared with 3 helper threads) and ships it (memcpy "
-                   "of one array overlapping the H2D of the previous), kernel, D2H, observation copied out while the rest lands")
+               api="DPVecEnv.step(actions, force_state=(qpos, qvel, contact)) with ordinary (pageable) numpy inputs and caller-owned "
+                   "outputs: dm_step_host copies the inputs into the handle's pinned block in chunks of whole tiles (copies shared "
+                   "with 3 helper threads); the step kernel of each chunk reads and writes the pinned block itself -- its TMA bulk "
+                   "loads / stores cross PCIe, both directions at once -- while the host copies the next chunk in and the previous "
+                   "chunk's observations out")
+    # the same call when the simulator keeps its state in the handle's pinned arrays (DPVecEnv.input_buffers()): no
+    # host-side staging at all, one kernel launch on mapped memory per step
+    qb, vb, cb, ab = env.input_buffers()
+    qb[...] = host["qpos"][0]; vb[...] = host["qvel"][0]; cb[...] = host["contact"][0]; ab[...] = host["action"][0]
+    env.copy_outputs = False
+    for i in range(warmup):
+        env.step(ab, force_state=(qb, vb, cb))
+    t0 = time.perf_counter()
+    for i in range(steps):
+        obs, rew, done, infos = env.step(ab, force_state=(qb, vb, cb))
+    dt = time.perf_counter() - t0
+    out["pinned"] = dict(value=args.envs * steps / dt, ms_per_step=1e3 * dt / steps,
+                         note="inputs written in place into DPVecEnv.input_buffers(), outputs read as views of the pinned block")
     env.close()
     return out
 

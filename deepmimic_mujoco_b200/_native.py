@@ -71,7 +71,7 @@ class ResetArgs(C.Structure):
 SYMBOLS = ["dm_abi_version", "dm_create", "dm_destroy", "dm_last_error", "dm_get_dims", "dm_get_model", "dm_fk_tables",
            "dm_upload_clips", "dm_compile_clips", "dm_get_compiled_clip", "dm_get_packed_rows", "dm_step", "dm_reset", "dm_step_host", "dm_reset_host", "dm_host_buffers",
            "dm_stats_zero", "dm_stats_device_ptr", "dm_stats_read", "dm_launch_count", "dm_step_kernel_time",
-           "dm_set_timing", "dm_set_kernel_variant", "dm_set_contact_mode", "dm_policy_upload", "dm_policy_set_normalizer",
+           "dm_set_timing", "dm_set_kernel_variant", "dm_set_contact_mode", "dm_set_host_mode", "dm_policy_upload", "dm_policy_set_normalizer",
            "dm_policy_normalizer_from_stats", "dm_policy_act", "dm_set_policy_variant"]
 
 _lib = None
@@ -110,6 +110,7 @@ def lib():
     L.dm_set_timing.argtypes = [C.c_void_p, C.c_int]
     L.dm_set_kernel_variant.argtypes = [C.c_void_p, C.c_int]
     L.dm_set_contact_mode.argtypes = [C.c_void_p, C.c_int]
+    L.dm_set_host_mode.argtypes = [C.c_void_p, C.c_int]
     L.dm_policy_upload.argtypes = [C.c_void_p, C.POINTER(Policy)]
     L.dm_policy_set_normalizer.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_float]
     L.dm_policy_normalizer_from_stats.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_void_p]

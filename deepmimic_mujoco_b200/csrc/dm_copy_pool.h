@@ -33,13 +33,37 @@ class CopyPool {
   CopyPool(const CopyPool&) = delete;
   CopyPool& operator=(const CopyPool&) = delete;
 
+  struct Seg {  // one memcpy(dst, src, bytes); src == NULL zero-fills
+    void* dst;
+    const void* src;
+    size_t bytes;
+  };
+  static constexpr int kMaxSegs = 16;
+
   // memcpy(dst, src, bytes), shared with the helpers when it is big enough to be worth a wake-up
   void copy(void* dst, const void* src, size_t bytes) {
-    if (threads_.empty() || bytes < kMinParallel) {
-      memcpy(dst, src, bytes);
+    const Seg s{dst, src, bytes};
+    copy_many(&s, 1);
+  }
+
+  // several copies as ONE job (the arrays of one chunk of a host step): a single wake-up and a single completion wait
+  // for all of them, pieces of every segment claimed from the same counter
+  void copy_many(const Seg* segs, int n) {
+    Job j{};
+    size_t total = 0;
+    for (int i = 0; i < n && j.n < kMaxSegs; ++i) {
+      if (!segs[i].bytes || !segs[i].dst) continue;
+      j.seg[j.n] = segs[i];
+      j.first[j.n] = j.chunks;
+      j.chunks += (segs[i].bytes + kChunk - 1) / kChunk;
+      total += segs[i].bytes;
+      ++j.n;
+    }
+    j.first[j.n] = j.chunks;
+    if (threads_.empty() || total < kMinParallel) {
+      for (int i = 0; i < j.n; ++i) one(j.seg[i].dst, j.seg[i].src, j.seg[i].bytes);
       return;
     }
-    Job j{(char*)dst, (const char*)src, bytes, (bytes + kChunk - 1) / kChunk};
     {
       // a helper that woke late may still hold a snapshot of the previous job (and would claim chunk numbers of this
       // one with it): publish only when none does.  Helpers take their snapshot under this mutex.
@@ -58,11 +82,17 @@ class CopyPool {
 
  private:
   struct Job {
-    char* dst;
-    const char* src;
-    size_t bytes, chunks;
+    Seg seg[kMaxSegs];
+    size_t first[kMaxSegs + 1];  // first piece number of every segment
+    size_t chunks;
+    int n;
   };
-  static constexpr size_t kChunk = 64 * 1024, kMinParallel = 192 * 1024;
+  static constexpr size_t kChunk = 32 * 1024, kMinParallel = 128 * 1024;
+  static constexpr int kSpinUs = 150;  // a host step's copy-in and copy-out jobs are one kernel (~70-100 us) apart
+  static void one(void* dst, const void* src, size_t bytes) {
+    if (src) memcpy(dst, src, bytes);
+    else memset(dst, 0, bytes);
+  }
   static void cpu_relax() {
 #if defined(__x86_64__) || defined(__i386__)
     __builtin_ia32_pause();
@@ -72,8 +102,11 @@ class CopyPool {
     for (;;) {
       const size_t c = next_.fetch_add(1, std::memory_order_relaxed);
       if (c >= j.chunks) return;
-      const size_t o = c * kChunk, len = o + kChunk <= j.bytes ? kChunk : j.bytes - o;
-      memcpy(j.dst + o, j.src + o, len);
+      int k = 0;
+      while (c >= j.first[k + 1]) ++k;
+      const Seg& g = j.seg[k];
+      const size_t o = (c - j.first[k]) * kChunk, len = o + kChunk <= g.bytes ? kChunk : g.bytes - o;
+      one((char*)g.dst + o, g.src ? (const char*)g.src + o : nullptr, len);
       done_.fetch_add(1, std::memory_order_release);
     }
   }
@@ -84,7 +117,7 @@ class CopyPool {
       const auto t0 = std::chrono::steady_clock::now();
       while (job_seq_.load(std::memory_order_acquire) == seen) {
         cpu_relax();
-        if (std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(60)) break;
+        if (std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(kSpinUs)) break;
       }
       Job j;
       {

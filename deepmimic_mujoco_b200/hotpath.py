@@ -340,5 +340,10 @@ class HotPath:
         """True: the floor-contact observation bits are derived from FK inside the kernels (include/dmhot.h)."""
         N.check(self.L.dm_set_contact_mode(self.h, 1 if from_fk else 0), self.h, "dm_set_contact_mode")
 
+    def set_host_mode(self, mapped):
+        """How step_host moves data: True = the kernel works on the pinned host block directly (default), False = copy
+        engines (H2D, kernel, D2H).  Same results."""
+        N.check(self.L.dm_set_host_mode(self.h, 1 if mapped else 0), self.h, "dm_set_host_mode")
+
     def set_kernel_variant(self, v):
         N.check(self.L.dm_set_kernel_variant(self.h, int(v)), self.h, "dm_set_kernel_variant")

@@ -17,6 +17,9 @@ Two data paths:
 """
 from __future__ import annotations
 
+import sys
+import ctypes as C
+
 import numpy as np
 
 from . import _native as N
@@ -52,6 +55,7 @@ class LazyInfos(list):
 
     def __init__(self, n):
         super().__init__([None] * n)
+        self._touched = []  # indices whose dict exists
 
     def __getitem__(self, i):
         v = list.__getitem__(self, i)
@@ -60,7 +64,16 @@ class LazyInfos(list):
         if v is None:
             v = {}
             list.__setitem__(self, i, v)
+            self._touched.append(i)
         return v
+
+    def _recycle(self):
+        """Back to n untouched entries (DPVecEnv hands a list out again once its previous holder has dropped it:
+        building n entries per step costs 17 us at 4096 environments and grows with n)."""
+        for i in self._touched:
+            list.__setitem__(self, i, None)
+        self._touched.clear()
+        return self
 
     def __iter__(self):
         for i in range(len(self)):
@@ -115,6 +128,34 @@ class DPVecEnv:
         self._force = None
         self.h2d_bytes = self.d2h_bytes = 0
         self._dev = None
+        # the argument block of dm_step_host, built once: the pinned slots never move, only the caller's arrays do
+        self._args = self.hp._step_args(n, pin["qpos"], pin["qvel"], pin["action"], pin["contact"], self.idx, self.ep_len, self.clip,
+                                        pin["obs"], self.reward, self.done, self.reason, self.torque, self.terms, self.ep_return,
+                                        0, False, None)
+        self._slot_ptr = {k: self._args_ptr(pin[k]) for k in ("qpos", "qvel", "action", "contact", "obs")}
+        self._h2d, self._d2h = C.c_int64(), C.c_int64()
+        self._call = (self.hp.L.dm_step_host, self.hp.h, C.byref(self._args), C.byref(self._h2d), C.byref(self._d2h))
+        # objects handed out by earlier steps; one that nobody references any more is handed out again
+        self._rings = {"obs": [], "rew": [], "done": [], "infos": []}
+        self._makers = {"obs": lambda: np.empty_like(pin["obs"]), "rew": lambda: np.empty_like(pin["reward"]),
+                        "done": lambda: np.empty(n, np.bool_), "infos": lambda: LazyInfos(n)}
+
+    @staticmethod
+    def _args_ptr(x):
+        return x.__array_interface__["data"][0]
+
+    def _fresh(self, kind):
+        """A caller-owned object for this step's observations / rewards / dones / infos.  Objects handed out earlier that
+        the caller has dropped (only the ring still references them) are reused: a fresh 1 MB array is a fresh mmap whose
+        pages fault in during the copy, which costs more than the copy itself, and a list of n entries costs O(n) to build."""
+        ring = self._rings[kind]
+        for a in ring:
+            if sys.getrefcount(a) == 3:  # the ring, the loop variable, getrefcount's argument
+                return a._recycle() if kind == "infos" else a
+        a = self._makers[kind]()
+        if len(ring) < 4:
+            ring.append(a)
+        return a
 
     def input_buffers(self):
         """The pinned (qpos, qvel, contact, action) arrays of the next step.  A simulator that writes its
@@ -178,22 +219,37 @@ class DPVecEnv:
             contact = self._into(p["contact"], fs[2])
         # copy_outputs: the observation goes straight into a fresh caller-owned array (copied inside dm_step_host while
         # the remaining outputs are still in flight); self.obs then aliases it until the next step
-        out_obs = np.empty_like(p["obs"]) if self.copy_outputs else p["obs"]
+        self.obs = None  # drop last step's array: if the caller did too, _fresh hands it out again
+        out_obs = self._fresh("obs") if self.copy_outputs else p["obs"]
         self.obs = out_obs
-        h2d, d2h = self.hp.step_host(n, qpos_in, qvel_in, self._actions, contact, self.idx, self.ep_len, self.clip,
-                                     out_obs, self.reward, self.done, self.reason, self.torque, self.terms, self.ep_return)
+        a, sp, ptr = self._args, self._slot_ptr, self._args_ptr
+        a.qpos = sp["qpos"] if qpos_in is p["qpos"] else ptr(qpos_in)
+        a.qvel = sp["qvel"] if qvel_in is p["qvel"] else ptr(qvel_in)
+        a.action = sp["action"] if self._actions is p["action"] else ptr(self._actions)
+        a.contact = None if contact is None else sp["contact"] if contact is p["contact"] else ptr(contact)
+        a.obs = sp["obs"] if out_obs is p["obs"] else ptr(out_obs)
+        fn, h, pa, ph, pd = self._call
+        rc = fn(h, pa, ph, pd)
+        if rc:
+            N.check(rc, h, "dm_step_host")
         self.qpos, self.qvel, self._actions = p["qpos"], p["qvel"], p["action"]  # the pinned copies, never the caller's arrays
-        self.h2d_bytes, self.d2h_bytes = h2d, d2h
+        self.h2d_bytes, self.d2h_bytes = self._h2d.value, self._d2h.value
         dones = self.done.view(np.bool_)
-        infos = LazyInfos(n)
+        infos = self._fresh("infos")
         if self.info_terms:
             for i in range(n):
                 if self.reason[i] != 8:
                     infos[i].update({k: float(self.terms[i, j]) for j, k in enumerate(N.TERM_NAMES[:5])})
-        rews = self.reward.copy() if self.copy_outputs else self.reward
+        if self.copy_outputs:
+            rews = self._fresh("rew")
+            np.copyto(rews, self.reward)
+        else:
+            rews = self.reward
         obs_out = out_obs if self.copy_outputs else self.obs
         if dones.any():
-            dones = dones.copy()
+            d2 = self._fresh("done")
+            np.copyto(d2, dones)
+            dones = d2
             ids = np.nonzero(dones)[0]
             ep_ret, ep_len, reasons = self.ep_return[ids].copy(), self.ep_len[ids].copy(), self.reason[ids].copy()
             self.terminal_obs[ids] = self.obs[ids]
@@ -208,7 +264,9 @@ class DPVecEnv:
                     info["done_reason"] = N.DONE_REASONS[reasons[k]]
                 info["episode"] = {"r": float(ep_ret[k]), "l": int(ep_len[k])}
         elif self.copy_outputs:
-            dones = dones.copy()
+            d2 = self._fresh("done")
+            np.copyto(d2, dones)
+            dones = d2
         return obs_out, rews, dones, infos
 
     def step(self, actions, force_state=None):

@@ -184,6 +184,14 @@ int dm_reset_host(dm_handle* h, const dm_reset_args* a);
  * one H2D transfer, the kernel, one D2H transfer.  (The reference's SubprocVecEnv pickles every observation
  * through a pipe instead, src/sb3_ppo.py:275-278.)  Valid until a call with a larger n or dm_destroy. */
 int dm_host_buffers(dm_handle* h, int32_t n, dm_step_args* out);
+/* How dm_step_host moves a batch of at least one tile (128 environments) between host and device:
+ *   DM_HOST_MAPPED  the step kernel reads and writes the pinned block of dm_host_buffers directly (its TMA bulk copies
+ *                   and stores cross PCIe, both directions at once); caller arrays that are not the pinned slots are
+ *                   staged in chunks of whole tiles, each chunk's kernel launched while the next is copied   [default]
+ *   DM_HOST_STAGED  copy engines: H2D into a device block, the kernel on device memory, D2H
+ * Same kernel and same results either way; batches smaller than a tile always take the staged form. */
+enum { DM_HOST_STAGED = 0, DM_HOST_MAPPED = 1 };
+int dm_set_host_mode(dm_handle* h, int mode);
 
 /* reward / observation-normaliser statistics (new functionality, no reference counterpart):
  * [count, sum r, sum r^2, n_done, sum ep_return(done), sum ep_len(done), sum obs[D], sum obs^2[D]] */

@@ -109,5 +109,20 @@ extern "C" int hh_copy_pool_selftest(int helpers, int iters, unsigned seed) {
     memcpy(ref.data() + off, src.data() + (it % 7), bytes);
     if (memcmp(dst.data() + off, ref.data() + off, bytes + 64) != 0) return it + 1;  // payload and the bytes behind it
   }
+  // several segments as one job (the arrays of one chunk of a host step), a zero-fill among them
+  for (int it = 0; it < iters / 4; ++it) {
+    dm::CopyPool::Seg segs[6];
+    size_t o = rnd() % 64;
+    for (size_t i = 0; i < dst.size(); ++i) dst[i] = ref[i] = (unsigned char)(it + i);
+    for (int k = 0; k < 6; ++k) {
+      const size_t bytes = k == 4 ? 0 : 1 + rnd() % (k == 1 ? 900000u : 90000u);
+      const unsigned char* sp = k == 3 ? nullptr : src.data() + (rnd() % 1000);
+      segs[k] = dm::CopyPool::Seg{dst.data() + o, sp, bytes};
+      if (sp) memcpy(ref.data() + o, sp, bytes); else memset(ref.data() + o, 0, bytes);
+      o += bytes + rnd() % 300;
+    }
+    pool.copy_many(segs, 6);
+    if (memcmp(dst.data(), ref.data(), dst.size()) != 0) return 100000 + it;
+  }
   return 0;
 }

@@ -89,6 +89,51 @@ def test_vecenv_pinned_inputs_are_zero_copy_and_equal():
     b.close()
 
 
+@pytest.mark.parametrize("n,combined,chunk", [(128, False, 0), (4096 + 37, False, 0), (2048 + 5, False, 256), (1024 + 3, True, 512)])
+def test_host_step_mapped_equals_staged(n, combined, chunk, monkeypatch):
+    """dm_step_host on the pinned block directly (DM_HOST_MAPPED: the kernel's TMA copies cross PCIe, caller arrays staged
+    in chunks of whole tiles over two streams) against the copy-engine form (DM_HOST_STAGED): the same kernel on other
+    addresses, so every output is bit-identical -- pageable caller arrays and in-place pinned arrays alike, ragged tail
+    (K1a on mapped memory) included."""
+    from deepmimic_mujoco_b200.vec_env import DPVecEnv
+    if chunk:
+        monkeypatch.setenv("DM_HOST_CHUNK", str(chunk))
+    rng = np.random.default_rng(n)
+    envs = [DPVecEnv(n, combined=combined, seed=3, copy_outputs=co) for co in (True, True, False)]
+    hp0 = envs[0].hp
+    m = hp0.mocaps[0]
+    d = hp0.dims
+    f = rng.integers(0, m.get_length(), n)
+    q = (np.asarray(m.data_config)[f] + rng.normal(0, 0.03, (n, d.nq))).astype(np.float32)
+    v = (np.asarray(m.data_vel)[f] + rng.normal(0, 0.4, (n, d.nv))).astype(np.float32)
+    q[::11, 2] -= 0.6
+    c = rng.integers(0, 256, n).astype(np.uint32)
+    lo, hi = envs[0].action_space.low, envs[0].action_space.high
+    act = rng.uniform(lo, hi, (n, d.na)).astype(np.float32)
+    frames = rng.integers(0, 40, n).astype(np.int32)
+    envs[0].hp.set_host_mode(False)
+    envs[1].hp.set_host_mode(True)
+    envs[2].hp.set_host_mode(True)
+    res = []
+    for k, e in enumerate(envs):
+        e.reset(frame=frames, coin=np.zeros(n, np.int32)) if combined else e.reset(frame=frames)
+        if k == 2:  # everything in place: one launch on the pinned block
+            qb, vb, cb, ab = e.input_buffers()
+            qb[...] = q; vb[...] = v; cb[...] = c; ab[...] = act
+            o, r, dn, _ = e.step(ab, force_state=(qb, vb, cb))
+        else:
+            o, r, dn, _ = e.step(act, force_state=(q, v, c))
+        res.append((np.array(o), np.array(r), np.array(dn), np.array(e.torque), np.array(e.idx), np.array(e.ep_len),
+                    np.array(e.clip), np.array(e.reason)))
+    assert combined or (res[0][2].any() and not res[0][2].all())
+    for other in res[1:]:
+        for x, y in zip(res[0], other):
+            np.testing.assert_array_equal(x, y)
+    assert envs[0].h2d_bytes == envs[1].h2d_bytes and envs[0].d2h_bytes == envs[1].d2h_bytes
+    for e in envs:
+        e.close()
+
+
 def test_lazy_infos_behaves_like_a_list_of_dicts():
     from deepmimic_mujoco_b200.vec_env import LazyInfos
     x = LazyInfos(5)
