@@ -197,11 +197,11 @@ __global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_co
     if (gt < 4) g_done[gt] = 0.0;
   }
   __syncthreads();
-  if (gt == 0) {  // fill the ring: every leader its own first tile, leader 0 the slots beyond the groups
-    if (group < nt) issue_load(group);
-    if (group == 0)
-      for (int j = n_groups; j < nbuf && j < nt; ++j) issue_load(j);
-  }
+  // Everything up to here, the clip table and the motor constants touch nothing an earlier launch writes.  Under
+  // programmatic dependent launch this prologue (and the launch latency in front of it) overlaps the tail of the
+  // previous kernel in the stream; griddepcontrol.wait then blocks until that kernel has completed and its writes
+  // (the in-out state of the previous step, the statistics) are visible.  Without the launch attribute both
+  // instructions are no-ops.
   if (TABLE_SMEM && tid == 0) {
     mbar_expect_tx(bars + TC::MAXBUF, sizeof(float) * x.table_floats);
     tma_load_1d(s_table, p.cs.rows, sizeof(float) * x.table_floats, bars + TC::MAXBUF);
@@ -217,6 +217,13 @@ __global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_co
     s_motor[k] = g;
     s_motor[TC::NUP + k] = lo;
     s_motor[2 * TC::NUP + k] = hi;
+  }
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (gt == 0) {  // fill the ring: every leader its own first tile, leader 0 the slots beyond the groups
+    if (group < nt) issue_load(group);
+    if (group == 0)
+      for (int j = n_groups; j < nbuf && j < nt; ++j) issue_load(j);
   }
   __syncthreads();
 

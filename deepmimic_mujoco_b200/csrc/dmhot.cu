@@ -63,6 +63,7 @@ struct dm_handle {
   cudaEvent_t obs_event = nullptr;
   cudaEvent_t chunk_event[16] = {};     // mapped host step: one per chunk in flight
   int host_mode = DM_HOST_MAPPED;       // DM_HOST_*; DM_HOST_MODE overrides
+  int pdl = 1;                          // programmatic dependent launch of the tile kernel (DM_PDL=0 turns it off)
   int host_trace = 0;                   // DM_HOST_TRACE: print the mean host time of every phase of the mapped step at destroy
   double ht[5] = {0, 0, 0, 0, 0};       // copy-in, launch, wait, copy-out, calls
   int host_chunk = 0;                   // environments per chunk of the mapped host step (0 = auto; DM_HOST_CHUNK)
@@ -136,6 +137,7 @@ extern "C" int dm_create(int device, int robot, int env_kind, dm_handle** out) {
   if (const char* e = getenv("DM_HOST_MODE")) h->host_mode = atoi(e) ? DM_HOST_MAPPED : DM_HOST_STAGED;
   if (const char* e = getenv("DM_HOST_CHUNK")) h->host_chunk = atoi(e);
   if (const char* e = getenv("DM_HOST_TRACE")) h->host_trace = atoi(e);
+  if (const char* e = getenv("DM_PDL")) h->pdl = atoi(e);
   dispatch(h, [&](auto rb, auto kind) -> int {
     using Rb = decltype(rb);
     using OL = ObsLayout<decltype(kind)::value, Rb>;
@@ -463,8 +465,19 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
       auto launch = [&](auto kern) -> cudaError_t {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        kern<<<grid, G * TC::TE, smem, s>>>(q, ex);
-        return cudaGetLastError();
+        // programmatic dependent launch: this kernel's launch latency and prologue (barriers, clip table, motor constants)
+        // overlap the tail of whatever runs before it in the stream; its griddepcontrol.wait orders everything else
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3(grid);
+        cfg.blockDim = dim3(G * TC::TE);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = s;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = h->pdl ? 1 : 0;
+        return cudaLaunchKernelEx(&cfg, kern, q, ex);
       };
       auto pick = [&](auto terms, auto stats) -> cudaError_t {
         constexpr bool T = decltype(terms)::value, S = decltype(stats)::value;
