@@ -138,10 +138,13 @@ struct TileIO {
 template <class Rb>
 struct KernelGroups {  // measured on humanoid3d: G = 5 (96 registers, ~330 B of spills) is 40 % slower than G = 4
   static constexpr int G = 4 * 128 / DM_TE;
+  // batches of at most WIDE_WANT tiles per SM run the instantiation compiled for GWIDE groups (no register cap)
+  static constexpr int GWIDE = 2, WIDE_WANT = 2;
 };
 template <>
 struct KernelGroups<Robot_unitree_g1> {  // 37 hinges: the joint blocks alone are 74 live registers when the tile is written
   static constexpr int G = 3 * 128 / DM_TE;  // measured at 1 M envs: G = 3 (168 regs) 407 us, G = 2 (254 regs, no spills) 484 us, G = 4 (128 regs) 462 us
+  static constexpr int GWIDE = 2, WIDE_WANT = 4;  // 65536 envs (3.5 tiles per SM): 29.1 us with two wide groups, 33.2 us with three
 };
 
 struct TileExtra {

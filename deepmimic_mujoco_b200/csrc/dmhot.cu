@@ -63,6 +63,7 @@ struct dm_handle {
   cudaEvent_t obs_event = nullptr;
   cudaEvent_t chunk_event[16] = {};     // mapped host step: one per chunk in flight
   int host_mode = DM_HOST_MAPPED;       // DM_HOST_*; DM_HOST_MODE overrides
+  int wide_override = -1;               // DM_WIDE=0: never use the two-group instantiation
   int pdl = 1;                          // programmatic dependent launch of the tile kernel (DM_PDL=0 turns it off)
   int host_trace = 0;                   // DM_HOST_TRACE: print the mean host time of every phase of the mapped step at destroy
   double ht[5] = {0, 0, 0, 0, 0};       // copy-in, launch, wait, copy-out, calls
@@ -138,6 +139,7 @@ extern "C" int dm_create(int device, int robot, int env_kind, dm_handle** out) {
   if (const char* e = getenv("DM_HOST_CHUNK")) h->host_chunk = atoi(e);
   if (const char* e = getenv("DM_HOST_TRACE")) h->host_trace = atoi(e);
   if (const char* e = getenv("DM_PDL")) h->pdl = atoi(e);
+  if (const char* e = getenv("DM_WIDE")) h->wide_override = atoi(e);
   dispatch(h, [&](auto rb, auto kind) -> int {
     using Rb = decltype(rb);
     using OL = ObsLayout<decltype(kind)::value, Rb>;
@@ -442,6 +444,12 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
       if (h->max_groups_override > 0 && h->max_groups_override < G) G = h->max_groups_override;
       const int want = (n_tiles + h->num_sms - 1) / h->num_sms;  // spread small batches over all SMs first
       G = want < G ? (want < 1 ? 1 : want) : G;
+      // Batches of a few tiles per SM cannot fill GMAX groups anyway: they run the instantiation compiled for two groups
+      // per CTA, whose threads get the registers they want (161-168 humanoid3d, 233-246 unitree_g1, no spills) instead of
+      // 128 / 168.  Measured (kernel time per step): humanoid3d 32768 envs 16.4 -> 11.4 us, 16384 envs 11.8 -> 11.2 us;
+      // G1 combined 65536 envs 33.2 -> 29.1 us; from ~1000 tiles on the occupancy of GMAX groups wins again.
+      const bool wide = !a->terms && h->wide_override != 0 && want <= KernelGroups<Rb>::WIDE_WANT && G >= 1;
+      if (wide && G > KernelGroups<Rb>::GWIDE) G = KernelGroups<Rb>::GWIDE;
       const int grid = (n_tiles + G - 1) / G < h->num_sms ? (n_tiles + G - 1) / G : h->num_sms;
       const int tiles_per_cta = (n_tiles + grid - 1) / grid;
       // ring slots: measured at 1 M / 4 M envs, slots beyond the groups (tiles loading while every group computes)
@@ -481,6 +489,10 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
       };
       auto pick = [&](auto terms, auto stats) -> cudaError_t {
         constexpr bool T = decltype(terms)::value, S = decltype(stats)::value;
+        if constexpr (!T) {
+          constexpr int GW = KernelGroups<Rb>::GWIDE;
+          if (wide) return table_smem ? launch(step_tile_kernel<KIND, Rb, T, S, true, GW>) : launch(step_tile_kernel<KIND, Rb, T, S, false, GW>);
+        }
         return table_smem ? launch(step_tile_kernel<KIND, Rb, T, S, true, GMAX>) : launch(step_tile_kernel<KIND, Rb, T, S, false, GMAX>);
       };
       using std::true_type; using std::false_type;
