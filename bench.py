@@ -314,13 +314,13 @@ def policy_time(hp, device, n):
     return res
 
 
-def e2e_region(args, steps, warmup, seed):
+def e2e_region(args, steps, warmup, seed, local_rank=0, world=1):
     """Same metric through the public API a user calls -- DPVecEnv.step(actions, force_state=(qpos, qvel, contact)) with
     HOST numpy buffers: H2D of the step's inputs, kernel, D2H of obs / reward / done / torque every step."""
     import torch
     from deepmimic_mujoco_b200.vec_env import DPVecEnv
-    env = DPVecEnv(args.envs, motion=args.motion.split(","), robot=args.robot, combined=args.combined, seed=seed)
-    dev = torch.device("cuda", 0)
+    env = DPVecEnv(args.envs, motion=args.motion.split(","), robot=args.robot, combined=args.combined, seed=seed, device=local_rank)
+    dev = torch.device("cuda", local_rank)
     B = 8
     s = synth_states(env.hp, args.envs, B, seed + 1, dev)
     host = {k: v.cpu().numpy() for k, v in s.items()}
@@ -331,17 +331,31 @@ def e2e_region(args, steps, warmup, seed):
         b = i % B
         return env.step(host["action"][b], force_state=(host["qpos"][b], host["qvel"][b], host["contact"][b]))
 
+    def over_ranks(dt):  # every rank steps its own environments at the same time; the job's time is the slowest rank's
+        if world == 1:
+            return dt
+        import torch.distributed as dist
+        t = torch.tensor([dt], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+
     for i in range(warmup):
         one(i)
-    torch.cuda.synchronize()
+    sync()
     t0 = time.perf_counter()
     for i in range(steps):
         obs, rew, done, infos = one(i)
     torch.cuda.synchronize()
-    dt = time.perf_counter() - t0
+    dt = over_ranks(time.perf_counter() - t0)
     assert obs.shape == (args.envs, env.hp.obs_dim) and len(infos) == args.envs
-    out = dict(value=args.envs * steps / dt, unit="env-steps/s", h2d_bytes_per_step=int(env.h2d_bytes),
-               d2h_bytes_per_step=int(env.d2h_bytes), ms_per_step=1e3 * dt / steps,
+    out = dict(value=world * args.envs * steps / dt, unit="env-steps/s", h2d_bytes_per_step=int(env.h2d_bytes) * world,
+               d2h_bytes_per_step=int(env.d2h_bytes) * world, ms_per_step=1e3 * dt / steps,
                api="DPVecEnv.step(actions, force_state=(qpos, qvel, contact)) with ordinary (pageable) numpy inputs and caller-owned "
                    "outputs: dm_step_host copies the inputs into the handle's pinned block in chunks of whole tiles (copies shared "
                    "with 3 helper threads); the step kernel of each chunk reads and writes the pinned block itself -- its TMA bulk "
@@ -354,11 +368,12 @@ def e2e_region(args, steps, warmup, seed):
     env.copy_outputs = False
     for i in range(warmup):
         env.step(ab, force_state=(qb, vb, cb))
+    sync()
     t0 = time.perf_counter()
     for i in range(steps):
         obs, rew, done, infos = env.step(ab, force_state=(qb, vb, cb))
-    dt = time.perf_counter() - t0
-    out["pinned"] = dict(value=args.envs * steps / dt, ms_per_step=1e3 * dt / steps,
+    dt = over_ranks(time.perf_counter() - t0)
+    out["pinned"] = dict(value=world * args.envs * steps / dt, ms_per_step=1e3 * dt / steps,
                          note="inputs written in place into DPVecEnv.input_buffers(), outputs read as views of the pinned block")
     env.close()
     return out
@@ -542,11 +557,13 @@ def main():
     if world > 1:
         import torch.distributed as dist
         dist.barrier()
+    if not args.no_e2e:  # every rank steps its own environments through the host API at the same time
+        del wl
+        torch.cuda.empty_cache()
+        e2e = e2e_region(args, min(args.steps, 200), 5, 7, local_rank, world)
+        if rank == 0:
+            line["e2e"] = e2e
     if rank == 0:
-        if not args.no_e2e:
-            del wl
-            torch.cuda.empty_cache()
-            line["e2e"] = e2e_region(args, min(args.steps, 200), 5, 7)
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline(args, args.cpu_seconds)
         RESULT.append(line)

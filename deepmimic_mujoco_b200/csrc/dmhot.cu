@@ -63,7 +63,7 @@ struct dm_handle {
   cudaEvent_t obs_event = nullptr;
   cudaEvent_t chunk_event[16] = {};     // mapped host step: one per chunk in flight
   int host_mode = DM_HOST_MAPPED;       // DM_HOST_*; DM_HOST_MODE overrides
-  int wide_override = -1;               // DM_WIDE=0: never use the two-group instantiation
+  int wide_override = -1;               // DM_WIDE=0: never use the two-group instantiation, 2: always
   int pdl = 1;                          // programmatic dependent launch of the tile kernel (DM_PDL=0 turns it off)
   int host_trace = 0;                   // DM_HOST_TRACE: print the mean host time of every phase of the mapped step at destroy
   double ht[5] = {0, 0, 0, 0, 0};       // copy-in, launch, wait, copy-out, calls
@@ -448,7 +448,7 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
       // per CTA, whose threads get the registers they want (161-168 humanoid3d, 233-246 unitree_g1, no spills) instead of
       // 128 / 168.  Measured (kernel time per step): humanoid3d 32768 envs 16.4 -> 11.4 us, 16384 envs 11.8 -> 11.2 us;
       // G1 combined 65536 envs 33.2 -> 29.1 us; from ~1000 tiles on the occupancy of GMAX groups wins again.
-      const bool wide = !a->terms && h->wide_override != 0 && want <= KernelGroups<Rb>::WIDE_WANT && G >= 1;
+      const bool wide = !a->terms && h->wide_override != 0 && (want <= KernelGroups<Rb>::WIDE_WANT || h->wide_override == 2);
       if (wide && G > KernelGroups<Rb>::GWIDE) G = KernelGroups<Rb>::GWIDE;
       const int grid = (n_tiles + G - 1) / G < h->num_sms ? (n_tiles + G - 1) / G : h->num_sms;
       const int tiles_per_cta = (n_tiles + grid - 1) / grid;
