@@ -140,11 +140,17 @@ struct KernelGroups {  // measured on humanoid3d: G = 5 (96 registers, ~330 B of
   static constexpr int G = 4 * 128 / DM_TE;
   // batches of at most WIDE_WANT tiles per SM run the instantiation compiled for GWIDE groups (no register cap)
   static constexpr int GWIDE = 2, WIDE_WANT = 2;
+  // in between, three groups at 164 registers (no spills) plus ONE lookahead ring slot beat four capped groups:
+  // 262144 envs 52.2 vs 55.5 us, 524288 envs 91.0 vs 94.8, 1 M envs 168.1 vs 172.7; at 4 M envs 639 vs 634 (four groups again)
+  static constexpr int GMID = 3, MID_WANT_LO = 8, MID_WANT_HI = 80, MID_NBUF = 4;
 };
 template <>
 struct KernelGroups<Robot_unitree_g1> {  // 37 hinges: the joint blocks alone are 74 live registers when the tile is written
   static constexpr int G = 3 * 128 / DM_TE;  // measured at 1 M envs: G = 3 (168 regs) 407 us, G = 2 (254 regs, no spills) 484 us, G = 4 (128 regs) 462 us
-  static constexpr int GWIDE = 2, WIDE_WANT = 4;  // 65536 envs (3.5 tiles per SM): 29.1 us with two wide groups, 33.2 us with three
+  // two wide groups against three capped ones: 65536 envs 29.1 vs 33.2 us, 131072 envs 52.7 vs 53.2, 262144 envs 87.0 vs 91.4,
+  // 1 M envs 320 vs 308 (a lookahead slot beside the two wide groups is far slower: 108 us at 262144 envs)
+  static constexpr int GWIDE = 2, WIDE_WANT = 16;
+  static constexpr int GMID = 0, MID_WANT_LO = 0, MID_WANT_HI = 0, MID_NBUF = 0;  // no middle shape
 };
 
 struct TileExtra {

@@ -450,11 +450,17 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
       // G1 combined 65536 envs 33.2 -> 29.1 us; from ~1000 tiles on the occupancy of GMAX groups wins again.
       const bool wide = !a->terms && h->wide_override != 0 && (want <= KernelGroups<Rb>::WIDE_WANT || h->wide_override == 2);
       if (wide && G > KernelGroups<Rb>::GWIDE) G = KernelGroups<Rb>::GWIDE;
+      // ... and some robots have a middle shape (KernelGroups::GMID groups without a register cap plus a lookahead slot)
+      using KG = KernelGroups<Rb>;
+      const bool mid = !wide && !a->terms && KG::GMID > 0 && h->wide_override != 0 && want >= KG::MID_WANT_LO && want <= KG::MID_WANT_HI &&
+                       G >= KG::GMID && h->max_groups_override == 0 && h->nbuf_override == 0 &&
+                       table_bytes + KG::MID_NBUF * TC::BUF_BYTES + KG::GMID * acc_bytes <= avail;  // only with the clip table in shared memory
+      if (mid) G = KG::GMID;
       const int grid = (n_tiles + G - 1) / G < h->num_sms ? (n_tiles + G - 1) / G : h->num_sms;
       const int tiles_per_cta = (n_tiles + grid - 1) / grid;
       // ring slots: measured at 1 M / 4 M envs, slots beyond the groups (tiles loading while every group computes)
       // are 3-5 % SLOWER than one slot per group, so the default ring is exactly the groups; DM_NBUF overrides
-      int nbuf_want = h->nbuf_override > 0 ? h->nbuf_override : G;
+      int nbuf_want = h->nbuf_override > 0 ? h->nbuf_override : (mid ? KG::MID_NBUF : G);
       nbuf_want = nbuf_want > TC::MAXBUF ? TC::MAXBUF : nbuf_want;
       nbuf_want = nbuf_want > tiles_per_cta ? tiles_per_cta : nbuf_want;  // no more slots than tiles
       nbuf_want = nbuf_want < G ? G : nbuf_want;
@@ -492,6 +498,10 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
         if constexpr (!T) {
           constexpr int GW = KernelGroups<Rb>::GWIDE;
           if (wide) return table_smem ? launch(step_tile_kernel<KIND, Rb, T, S, true, GW>) : launch(step_tile_kernel<KIND, Rb, T, S, false, GW>);
+          if constexpr (KernelGroups<Rb>::GMID > 0) {
+            constexpr int GM = KernelGroups<Rb>::GMID;
+            if (mid) return table_smem ? launch(step_tile_kernel<KIND, Rb, T, S, true, GM>) : launch(step_tile_kernel<KIND, Rb, T, S, false, GM>);
+          }
         }
         return table_smem ? launch(step_tile_kernel<KIND, Rb, T, S, true, GMAX>) : launch(step_tile_kernel<KIND, Rb, T, S, false, GMAX>);
       };

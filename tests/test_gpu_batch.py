@@ -64,6 +64,29 @@ def test_tile_kernel_equals_strided_kernel(robot, motion, combined):
 
 
 @pytest.mark.parametrize("robot,motion,combined", CASES)
+def test_launch_shapes_agree(robot, motion, combined, monkeypatch):
+    """The same batch through every launch shape of the tile kernel: the two-group instantiation small batches get (no
+    register cap), the capped one large batches get (DM_WIDE=0), and without programmatic dependent launch (DM_PDL=0);
+    statistics included.  Same arithmetic, so integers and flags agree exactly and floats to an ulp or two."""
+    n = 128 * 40
+    res = []
+    for env in ({}, {"DM_WIDE": "0"}, {"DM_PDL": "0"}):
+        for k in ("DM_WIDE", "DM_PDL"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)  # read when the handle is created
+        hp, s = _make(robot, motion, combined, n)
+        res.append(_run(hp, s, 1, stats=True))
+        hp.close()
+    for other in res[1:]:
+        for k in res[0]:
+            if res[0][k].dtype.kind == "f":
+                np.testing.assert_allclose(res[0][k], other[k], rtol=2e-6, atol=2e-7, err_msg=k)
+            else:
+                np.testing.assert_array_equal(res[0][k], other[k], err_msg=k)
+
+
+@pytest.mark.parametrize("robot,motion,combined", CASES)
 def test_random_batch_matches_oracle(robot, motion, combined):
     from oracle.envs import MultiClipEnv, SingleClipEnv
     n = 256
