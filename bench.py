@@ -27,10 +27,12 @@ sys.path.insert(0, REPO)
 BYTES_PER_ENV_STEP = {("humanoid3d", 0): 793, ("unitree_g1", 0): 953, ("unitree_g1", 1): 1021}
 L2_BYTES = 126e6
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE step-kernel launch from `ncu --set full` captures of this very
-# command (profiles/r01_step_tile_v3_*_ncu_full_summary.txt), keyed by (robot, env kind, envs per GPU); at 4096 envs the
+# command (profiles/r01_step_tile_s18_*_ncu_full_summary.txt), keyed by (robot, env kind, envs per GPU); at 4096 envs the
 # 1.7 MB of outputs are still dirty in L2 when the kernel ends, so only the reads reach DRAM inside the launch
-NCU_TRAFFIC = {("humanoid3d", 0, 4096): (1.764864e6, "profiles/r01_step_tile_v3_4096_ncu_full_summary.txt"),
-               ("humanoid3d", 0, 1048576): (430.431744e6 + 365.887744e6, "profiles/r01_step_tile_v3_1M_ncu_full_summary.txt")}
+NCU_TRAFFIC = {("humanoid3d", 0, 4096): (1.764096e6, "profiles/r01_step_tile_s18_h4096_ncu_full_summary.txt"),
+               ("humanoid3d", 0, 1048576): (428.022528e6 + 362.629888e6, "profiles/r01_step_tile_s18_h1M_ncu_full_summary.txt"),
+               ("unitree_g1", 1, 1048576): (484.514816e6 + 536.993536e6, "profiles/r01_step_tile_s18_g1c_1M_ncu_full_summary.txt"),
+               ("unitree_g1", 1, 262144): (120.834560e6 + 94.626048e6, "profiles/r01_step_tile_s18_g1c_262144_ncu_full_summary.txt")}
 
 
 def parse():
