@@ -361,8 +361,8 @@ def e2e_region(args, steps, warmup, seed, local_rank=0, world=1):
                api="DPVecEnv.step(actions, force_state=(qpos, qvel, contact)) with ordinary (pageable) numpy inputs and caller-owned "
                    "outputs: dm_step_host copies the inputs into the handle's pinned block in chunks of whole tiles (copies shared "
                    "with 3 helper threads); the step kernel of each chunk reads and writes the pinned block itself -- its TMA bulk "
-                   "loads / stores cross PCIe, both directions at once -- while the host copies the next chunk in and the previous "
-                   "chunk's observations out")
+                   "loads / stores cross PCIe, both directions at once -- while the host copies the next chunk in; the observations "
+                   "land directly in the (pinned, recycled) array the caller receives")
     # the same call when the simulator keeps its state in the handle's pinned arrays (DPVecEnv.input_buffers()): no
     # host-side staging at all, one kernel launch on mapped memory per step
     qb, vb, cb, ab = env.input_buffers()

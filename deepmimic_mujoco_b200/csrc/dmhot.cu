@@ -677,12 +677,31 @@ static int step_host_mapped(dm_handle* h, const dm_step_args* a, const StepStage
   const size_t n = a->n;
   if (!h->host_stream2) CU(h, cudaStreamCreateWithFlags(&h->host_stream2, cudaStreamNonBlocking));
   struct Arr { void* slot; const void* src; void* dst; size_t row; };  // src: caller input (or NULL), dst: caller output (or NULL)
-  const Arr ins[] = {{g.hq, a->qpos, nullptr, sizeof(float) * d.nq}, {g.hv, a->qvel, nullptr, sizeof(float) * d.nv},
-                     {g.ha, a->action, nullptr, sizeof(float) * d.na}, {g.hc, a->contact, nullptr, 4},
+  // A big caller array that is itself pinned host memory (cudaHostAlloc / cudaHostRegister: torch pin_memory(), DPVecEnv's
+  // own output arrays) needs no staging either: the kernel works on it where it lies.
+  float *bq = g.hq, *bv = g.hv, *ba = g.ha, *bo = g.ho, *bt = g.ht;
+  auto direct = [&](const void* p, size_t bytes) -> float* {
+    if (!p || bytes < 64 * 1024 || (reinterpret_cast<uintptr_t>(p) & 15u)) return nullptr;
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+      cudaGetLastError();
+      return nullptr;
+    }
+    return at.type == cudaMemoryTypeHost ? (float*)at.devicePointer : nullptr;
+  };
+  const void *cq = a->qpos, *cv = a->qvel, *ca = a->action;
+  void *co = a->obs, *ct = a->torque;
+  if (cq != g.hq) if (float* q = direct(cq, sizeof(float) * n * d.nq)) { bq = q; cq = q; }
+  if (cv != g.hv) if (float* q = direct(cv, sizeof(float) * n * d.nv)) { bv = q; cv = q; }
+  if (ca != g.ha) if (float* q = direct(ca, sizeof(float) * n * d.na)) { ba = q; ca = q; }
+  if (co != g.ho) if (float* q = direct(co, sizeof(float) * n * d.obs_dim)) { bo = q; co = q; }
+  if (ct && ct != g.ht) if (float* q = direct(ct, sizeof(float) * n * d.nu)) { bt = q; ct = q; }
+  const Arr ins[] = {{bq, cq, nullptr, sizeof(float) * d.nq}, {bv, cv, nullptr, sizeof(float) * d.nv},
+                     {ba, ca, nullptr, sizeof(float) * d.na}, {g.hc, a->contact, nullptr, 4},
                      {g.hi, a->idx, nullptr, 4}, {g.hl, a->ep_len, nullptr, 4}, {g.hk, a->clip, nullptr, 4},
                      {g.her, a->ep_return, nullptr, 4}};
-  const Arr outs[] = {{g.ho, nullptr, a->obs, sizeof(float) * d.obs_dim}, {g.hr, nullptr, a->reward, 4}, {g.hd, nullptr, a->done, 1},
-                      {g.hz, nullptr, a->reason, 1}, {g.ht, nullptr, a->torque, sizeof(float) * d.nu},
+  const Arr outs[] = {{bo, nullptr, co, sizeof(float) * d.obs_dim}, {g.hr, nullptr, a->reward, 4}, {g.hd, nullptr, a->done, 1},
+                      {g.hz, nullptr, a->reason, 1}, {bt, nullptr, ct, sizeof(float) * d.nu},
                       {g.hm, nullptr, a->terms, sizeof(float) * DM_NTERMS}, {g.hi, nullptr, a->idx, 4}, {g.hl, nullptr, a->ep_len, 4},
                       {g.hk, nullptr, a->clip, 4}, {g.her, nullptr, a->ep_return, 4}};
   bool staged_any = false;
@@ -733,10 +752,10 @@ static int step_host_mapped(dm_handle* h, const dm_step_args* a, const StepStage
     lap(0);
     dm_step_args k = *a;
     k.n = (int32_t)m;
-    k.qpos = g.hq + e0 * d.nq; k.qvel = g.hv + e0 * d.nv; k.action = g.ha + e0 * d.na; k.contact = g.hc + e0;
+    k.qpos = bq + e0 * d.nq; k.qvel = bv + e0 * d.nv; k.action = ba + e0 * d.na; k.contact = g.hc + e0;
     k.idx = g.hi + e0; k.ep_len = g.hl + e0; k.clip = g.hk + e0;
-    k.obs = g.ho + e0 * d.obs_dim; k.reward = g.hr + e0; k.done = g.hd + e0; k.reason = g.hz + e0;
-    k.torque = a->torque ? g.ht + e0 * d.nu : nullptr;
+    k.obs = bo + e0 * d.obs_dim; k.reward = g.hr + e0; k.done = g.hd + e0; k.reason = g.hz + e0;
+    k.torque = a->torque ? bt + e0 * d.nu : nullptr;
     k.terms = a->terms ? g.hm + e0 * DM_NTERMS : nullptr;
     k.ep_return = a->ep_return ? g.her + e0 : nullptr;
     cudaStream_t s = (c & 1) ? h->host_stream2 : h->host_stream;

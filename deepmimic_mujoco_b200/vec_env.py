@@ -137,12 +137,22 @@ class DPVecEnv:
         self._call = (self.hp.L.dm_step_host, self.hp.h, C.byref(self._args), C.byref(self._h2d), C.byref(self._d2h))
         # objects handed out by earlier steps; one that nobody references any more is handed out again
         self._rings = {"obs": [], "rew": [], "done": [], "infos": []}
-        self._makers = {"obs": lambda: np.empty_like(pin["obs"]), "rew": lambda: np.empty_like(pin["reward"]),
+        self._makers = {"obs": self._new_obs_array, "rew": lambda: np.empty_like(pin["reward"]),
                         "done": lambda: np.empty(n, np.bool_), "infos": lambda: LazyInfos(n)}
 
     @staticmethod
     def _args_ptr(x):
         return x.__array_interface__["data"][0]
+
+    def _new_obs_array(self):
+        """A caller-owned observation array.  The ones that live in the reuse ring are PINNED host memory: dm_step_host
+        then lets the kernel write the observations straight into them (no copy out of the staging block).  Once the
+        ring is full (the caller keeps more than four steps of observations alive) further arrays are ordinary ones."""
+        shape = self._pin["obs"].shape
+        if len(self._rings["obs"]) < 4:
+            import torch
+            return torch.empty(shape, dtype=torch.float32, pin_memory=True).numpy()
+        return np.empty(shape, np.float32)
 
     def _fresh(self, kind):
         """A caller-owned object for this step's observations / rewards / dones / infos.  Objects handed out earlier that

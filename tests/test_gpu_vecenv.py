@@ -99,7 +99,8 @@ def test_host_step_mapped_equals_staged(n, combined, chunk, monkeypatch):
     if chunk:
         monkeypatch.setenv("DM_HOST_CHUNK", str(chunk))
     rng = np.random.default_rng(n)
-    envs = [DPVecEnv(n, combined=combined, seed=3, copy_outputs=co) for co in (True, True, False)]
+    import torch
+    envs = [DPVecEnv(n, combined=combined, seed=3, copy_outputs=co) for co in (True, True, False, True)]
     hp0 = envs[0].hp
     m = hp0.mocaps[0]
     d = hp0.dims
@@ -114,6 +115,8 @@ def test_host_step_mapped_equals_staged(n, combined, chunk, monkeypatch):
     envs[0].hp.set_host_mode(False)
     envs[1].hp.set_host_mode(True)
     envs[2].hp.set_host_mode(True)
+    envs[3].hp.set_host_mode(True)
+    pin = lambda x: torch.from_numpy(x).pin_memory().numpy()  # caller arrays that are themselves pinned: used where they lie
     res = []
     for k, e in enumerate(envs):
         e.reset(frame=frames, coin=np.zeros(n, np.int32)) if combined else e.reset(frame=frames)
@@ -121,6 +124,8 @@ def test_host_step_mapped_equals_staged(n, combined, chunk, monkeypatch):
             qb, vb, cb, ab = e.input_buffers()
             qb[...] = q; vb[...] = v; cb[...] = c; ab[...] = act
             o, r, dn, _ = e.step(ab, force_state=(qb, vb, cb))
+        elif k == 3:
+            o, r, dn, _ = e.step(pin(act), force_state=(pin(q), pin(v), c))
         else:
             o, r, dn, _ = e.step(act, force_state=(q, v, c))
         res.append((np.array(o), np.array(r), np.array(dn), np.array(e.torque), np.array(e.idx), np.array(e.ep_len),
