@@ -562,7 +562,7 @@ def main():
     if not args.no_e2e:  # every rank steps its own environments through the host API at the same time
         del wl
         torch.cuda.empty_cache()
-        e2e = e2e_region(args, min(args.steps, 200), 5, 7, local_rank, world)
+        e2e = e2e_region(args, min(args.steps, 200), 20, 7, local_rank, world)
         if rank == 0:
             line["e2e"] = e2e
     if rank == 0:

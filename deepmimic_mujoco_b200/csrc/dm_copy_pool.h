@@ -88,7 +88,7 @@ class CopyPool {
     int n;
   };
   static constexpr size_t kChunk = 32 * 1024, kMinParallel = 128 * 1024;
-  static constexpr int kSpinUs = 150;  // a host step's copy-in and copy-out jobs are one kernel (~70-100 us) apart
+  static constexpr int kSpinUs = 400;  // a host step copies in at its start and (sometimes) out at its end, ~100-300 us apart; helpers that fell asleep in between wake too late to help
   static void one(void* dst, const void* src, size_t bytes) {
     if (src) memcpy(dst, src, bytes);
     else memset(dst, 0, bytes);
