@@ -250,7 +250,8 @@ template <class IO>
 struct io_zeroes_on_guard<IO, std::enable_if_t<!IO::kZeroOnGuard>> : std::false_type {};
 
 // ---- one environment step --------------------------------------------------------------------
-template <int KIND, class Rb, class IO, bool WANT_TERMS>
+// ROW_GIVEN: `rows` already points at THIS environment's packed row (the tile kernel staged it in shared memory)
+template <int KIND, class Rb, class IO, bool WANT_TERMS, bool ROW_GIVEN = false>
 DM_HD void env_step(IO& io, const ClipSet& cs, const float* __restrict__ rows, EnvState& st, uint32_t contact, StepOut& so) {
   using RL = RowLayout<Rb>;
   using OL = ObsLayout<KIND, Rb>;
@@ -258,7 +259,7 @@ DM_HD void env_step(IO& io, const ClipSet& cs, const float* __restrict__ rows, E
   const ClipDesc cd = cs.clip[clip0];
   const int frame = (KIND == KIND_SINGLE) ? st.idx : (st.idx % cd.len);
   const int row_i = cd.row0 + (cd.fixed_row >= 0 ? cd.fixed_row : frame);
-  const float* __restrict__ row = rows + size_t(row_i) * RL::STRIDE;
+  const float* __restrict__ row = ROW_GIVEN ? rows : rows + size_t(row_i) * RL::STRIDE;
 
   write_torque<Rb>(io);
 

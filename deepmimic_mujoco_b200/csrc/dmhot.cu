@@ -63,6 +63,7 @@ struct dm_handle {
   cudaEvent_t obs_event = nullptr;
   cudaEvent_t chunk_event[16] = {};     // mapped host step: one per chunk in flight
   int host_mode = DM_HOST_MAPPED;       // DM_HOST_*; DM_HOST_MODE overrides
+  int row_stage_override = -1;          // DM_ROW_STAGE=0: never stage per-environment rows
   int wide_override = -1;               // DM_WIDE=0: never use the two-group instantiation, 2: always
   int pdl = 1;                          // programmatic dependent launch of the tile kernel (DM_PDL=0 turns it off)
   int host_trace = 0;                   // DM_HOST_TRACE: print the mean host time of every phase of the mapped step at destroy
@@ -140,6 +141,7 @@ extern "C" int dm_create(int device, int robot, int env_kind, dm_handle** out) {
   if (const char* e = getenv("DM_HOST_TRACE")) h->host_trace = atoi(e);
   if (const char* e = getenv("DM_PDL")) h->pdl = atoi(e);
   if (const char* e = getenv("DM_WIDE")) h->wide_override = atoi(e);
+  if (const char* e = getenv("DM_ROW_STAGE")) h->row_stage_override = atoi(e);
   dispatch(h, [&](auto rb, auto kind) -> int {
     using Rb = decltype(rb);
     using OL = ObsLayout<decltype(kind)::value, Rb>;
@@ -474,7 +476,12 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
       bool table_smem = nb_table >= G && (nb_table >= nb_plain || nb_table >= G + 1);
       if (h->table_smem_override >= 0) table_smem = h->table_smem_override != 0 && nb_table >= G;
       const int nbuf = table_smem ? nb_table : nb_plain;
-      const size_t smem = TC::FIXED_BYTES + (table_smem ? table_bytes : 0) + (size_t)nbuf * TC::BUF_BYTES + G * acc_bytes;
+      size_t smem = TC::FIXED_BYTES + (table_smem ? table_bytes : 0) + (size_t)nbuf * TC::BUF_BYTES + G * acc_bytes;
+      // a table that stays in global memory: in the wide shape there is room to stage every environment's own row a tile ahead
+      const size_t row_stage_bytes = (size_t)G * TC::TE * RowLayout<Rb>::STRIDE * sizeof(float);
+      const bool row_stage = wide && !table_smem && !h->skip_compute && h->row_stage_override != 0 && G <= 3 &&
+                             smem + row_stage_bytes <= TC::SMEM_BUDGET;
+      if (row_stage) smem += row_stage_bytes;
       TileExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float)), nbuf, h->skip_compute};
       auto launch = [&](auto kern) -> cudaError_t {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -497,6 +504,7 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
         constexpr bool T = decltype(terms)::value, S = decltype(stats)::value;
         if constexpr (!T) {
           constexpr int GW = KernelGroups<Rb>::GWIDE;
+          if (wide && row_stage) return launch(step_tile_kernel<KIND, Rb, T, S, 2, GW>);
           if (wide) return table_smem ? launch(step_tile_kernel<KIND, Rb, T, S, true, GW>) : launch(step_tile_kernel<KIND, Rb, T, S, false, GW>);
           if constexpr (KernelGroups<Rb>::GMID > 0) {
             constexpr int GM = KernelGroups<Rb>::GMID;

@@ -66,12 +66,13 @@ def test_tile_kernel_equals_strided_kernel(robot, motion, combined):
 @pytest.mark.parametrize("robot,motion,combined", CASES)
 def test_launch_shapes_agree(robot, motion, combined, monkeypatch):
     """The same batch through every launch shape of the tile kernel: the two-group instantiation small batches get (no
-    register cap), the capped one large batches get (DM_WIDE=0), and without programmatic dependent launch (DM_PDL=0);
+    register cap), the capped one large batches get (DM_WIDE=0), without programmatic dependent launch (DM_PDL=0), and without
+    the per-environment row stage that tables too big for shared memory get (DM_ROW_STAGE=0; G1 combined);
     statistics included.  Same arithmetic, so integers and flags agree exactly and floats to an ulp or two."""
     n = 128 * 40
     res = []
-    for env in ({}, {"DM_WIDE": "0"}, {"DM_PDL": "0"}):
-        for k in ("DM_WIDE", "DM_PDL"):
+    for env in ({}, {"DM_WIDE": "0"}, {"DM_PDL": "0"}, {"DM_ROW_STAGE": "0"}):
+        for k in ("DM_WIDE", "DM_PDL", "DM_ROW_STAGE"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)  # read when the handle is created
