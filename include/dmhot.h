@@ -174,14 +174,17 @@ int dm_get_packed_rows(const dm_handle* h, float* rows, int32_t* total_rows);
 int dm_step(dm_handle* h, const dm_step_args* a);
 int dm_reset(dm_handle* h, const dm_reset_args* a);
 
-/* same, HOST pointers, AoS only: H2D copies, kernel, D2H copies, stream sync.  h2d/d2h (may be NULL)
- * receive the bytes moved. */
+/* same, HOST pointers, AoS only; returns when the outputs are in the caller's arrays.  Batches of at least one
+ * tile run in the mode of dm_set_host_mode (default: the kernel works on pinned host memory directly -- the handle's
+ * block, or the caller's own arrays where those are pinned); smaller ones by H2D copies, kernel, D2H copies.
+ * h2d/d2h (may be NULL) receive the bytes that cross PCIe. */
 int dm_step_host(dm_handle* h, const dm_step_args* a, int64_t* h2d_bytes, int64_t* d2h_bytes);
 int dm_reset_host(dm_handle* h, const dm_reset_args* a);
 /* Pinned host buffers for n environments, laid out exactly as dm_step_host stages them: every pointer field of
  * *out (qpos ... reason, incl. torque / terms / ep_return) receives a HOST pointer owned by the handle.  A caller
  * that keeps its per-step arrays there and passes those very pointers to dm_step_host pays no staging copies --
- * one H2D transfer, the kernel, one D2H transfer.  (The reference's SubprocVecEnv pickles every observation
+ * one kernel launch on the mapped block (DM_HOST_MAPPED), or one H2D transfer, the kernel, one D2H transfer
+ * (DM_HOST_STAGED).  (The reference's SubprocVecEnv pickles every observation
  * through a pipe instead, src/sb3_ppo.py:275-278.)  Valid until a call with a larger n or dm_destroy. */
 int dm_host_buffers(dm_handle* h, int32_t n, dm_step_args* out);
 /* How dm_step_host moves a batch of at least one tile (128 environments) between host and device:
