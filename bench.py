@@ -30,9 +30,9 @@ L2_BYTES = 126e6
 # command (profiles/r01_step_tile_s18_*_ncu_full_summary.txt), keyed by (robot, env kind, envs per GPU); at 4096 envs the
 # 1.7 MB of outputs are still dirty in L2 when the kernel ends, so only the reads reach DRAM inside the launch
 NCU_TRAFFIC = {("humanoid3d", 0, 4096): (1.764096e6, "profiles/r01_step_tile_s18_h4096_ncu_full_summary.txt"),
-               ("humanoid3d", 0, 1048576): (428.022528e6 + 362.629888e6, "profiles/r01_step_tile_s18_h1M_ncu_full_summary.txt"),
-               ("unitree_g1", 1, 1048576): (484.514816e6 + 536.993536e6, "profiles/r01_step_tile_s18_g1c_1M_ncu_full_summary.txt"),
-               ("unitree_g1", 1, 262144): (120.834560e6 + 94.626048e6, "profiles/r01_step_tile_s18_g1c_262144_ncu_full_summary.txt")}
+               ("humanoid3d", 0, 1048576): (427.913216e6 + 362.767616e6, "profiles/r01_step_tile_s18_h1M_ncu_full_summary.txt"),
+               ("unitree_g1", 1, 1048576): (484.756480e6 + 535.972096e6, "profiles/r01_step_tile_s18_g1c_1M_ncu_full_summary.txt"),
+               ("unitree_g1", 1, 262144): (120.824832e6 + 95.611392e6, "profiles/r01_step_tile_s18_g1c_262144_ncu_full_summary.txt")}
 
 
 def parse():
