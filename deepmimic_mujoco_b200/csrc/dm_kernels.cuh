@@ -232,7 +232,7 @@ __device__ __forceinline__ double warp_sum(double v) {
 }
 
 // blockDim = (32, 8): threadIdx.x walks environments, each block reduces a slab of environments
-__global__ void __launch_bounds__(256) stats_kernel(const StatsParams p) {
+static __global__ void __launch_bounds__(256) stats_kernel(const StatsParams p) {
   const int lane = threadIdx.x, wy = threadIdx.y;
   const int per_block = (p.n + gridDim.x - 1) / gridDim.x;
   const int e0 = blockIdx.x * per_block, e1 = min(p.n, e0 + per_block);

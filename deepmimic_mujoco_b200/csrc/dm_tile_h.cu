@@ -1,0 +1,11 @@
+// Tile-kernel instantiations of one (environment kind, robot) pair; see dm_tile_launch.cuh.
+#include <type_traits>
+#define DM_TILE_LAUNCH_IMPL
+#include "dm_tile_launch.cuh"
+
+namespace dm {
+template <>
+cudaError_t launch_tile<KIND_SINGLE, Robot_humanoid3d>(const TileLaunch& c, const StepParams& q, const TileExtra& ex) {
+  return launch_tile_impl<KIND_SINGLE, Robot_humanoid3d>(c, q, ex);
+}
+}  // namespace dm

@@ -12,7 +12,7 @@
 
 #include "../../include/dmhot.h"
 #include "dm_kernels.cuh"
-#include "dm_tile_kernel.cuh"
+#include "dm_tile_launch.cuh"
 #include "dm_pack.h"
 #include <chrono>
 #include "dm_copy_pool.h"
@@ -483,39 +483,10 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
                              smem + row_stage_bytes <= TC::SMEM_BUDGET;
       if (row_stage) smem += row_stage_bytes;
       TileExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float)), nbuf, h->skip_compute};
-      auto launch = [&](auto kern) -> cudaError_t {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        // programmatic dependent launch: this kernel's launch latency and prologue (barriers, clip table, motor constants)
-        // overlap the tail of whatever runs before it in the stream; its griddepcontrol.wait orders everything else
-        cudaLaunchConfig_t cfg{};
-        cfg.gridDim = dim3(grid);
-        cfg.blockDim = dim3(G * TC::TE);
-        cfg.dynamicSmemBytes = smem;
-        cfg.stream = s;
-        cudaLaunchAttribute at[1];
-        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        at[0].val.programmaticStreamSerializationAllowed = 1;
-        cfg.attrs = at;
-        cfg.numAttrs = h->pdl ? 1 : 0;
-        return cudaLaunchKernelEx(&cfg, kern, q, ex);
-      };
-      auto pick = [&](auto terms, auto stats) -> cudaError_t {
-        constexpr bool T = decltype(terms)::value, S = decltype(stats)::value;
-        if constexpr (!T) {
-          constexpr int GW = KernelGroups<Rb>::GWIDE;
-          if (wide && row_stage) return launch(step_tile_kernel<KIND, Rb, T, S, 2, GW>);
-          if (wide) return table_smem ? launch(step_tile_kernel<KIND, Rb, T, S, true, GW>) : launch(step_tile_kernel<KIND, Rb, T, S, false, GW>);
-          if constexpr (KernelGroups<Rb>::GMID > 0) {
-            constexpr int GM = KernelGroups<Rb>::GMID;
-            if (mid) return table_smem ? launch(step_tile_kernel<KIND, Rb, T, S, true, GM>) : launch(step_tile_kernel<KIND, Rb, T, S, false, GM>);
-          }
-        }
-        return table_smem ? launch(step_tile_kernel<KIND, Rb, T, S, true, GMAX>) : launch(step_tile_kernel<KIND, Rb, T, S, false, GMAX>);
-      };
-      using std::true_type; using std::false_type;
-      cudaError_t e = a->terms ? (a->accumulate_stats ? pick(true_type{}, true_type{}) : pick(true_type{}, false_type{}))
-                               : (a->accumulate_stats ? pick(false_type{}, true_type{}) : pick(false_type{}, false_type{}));
+      // the kernels themselves live in dm_tile_{h,g,c}.cu, one translation unit per (kind, robot)
+      TileLaunch tl{grid, G, smem, s, h->pdl != 0, a->terms != nullptr, a->accumulate_stats != 0,
+                    row_stage ? 2 : (table_smem ? 1 : 0), wide ? 1 : (mid ? 2 : 0)};
+      cudaError_t e = launch_tile<KIND, Rb>(tl, q, ex);
       CU(h, e);
       h->launches++;
     }
