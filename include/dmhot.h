@@ -192,7 +192,9 @@ int dm_host_buffers(dm_handle* h, int32_t n, dm_step_args* out);
  *                   and stores cross PCIe, both directions at once); caller arrays that are not the pinned slots are
  *                   staged in chunks of whole tiles, each chunk's kernel launched while the next is copied   [default]
  *   DM_HOST_STAGED  copy engines: H2D into a device block, the kernel on device memory, D2H
- * Same kernel and same results either way; batches smaller than a tile always take the staged form. */
+ * Same kernel and same results either way; batches smaller than a tile always take the staged form.
+ * dm_reset_host follows the same mode: mapped, the reset kernel works on the pinned memory and only the rows of the
+ * environments being reset cross PCIe. */
 enum { DM_HOST_STAGED = 0, DM_HOST_MAPPED = 1 };
 int dm_set_host_mode(dm_handle* h, int mode);
 
