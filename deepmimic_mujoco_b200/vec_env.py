@@ -133,6 +133,9 @@ class DPVecEnv:
                                         pin["obs"], self.reward, self.done, self.reason, self.torque, self.terms, self.ep_return,
                                         0, False, None)
         self._slot_ptr = {k: self._args_ptr(pin[k]) for k in ("qpos", "qvel", "action", "contact", "obs")}
+        # ... and of the auto-reset (dm_reset_host): only the mask, the observation array and the RNG counter change
+        self._rargs = self.hp._reset_args(n, None, None, None, None, pin["qpos"], pin["qvel"], self.idx, self.ep_len, self.clip,
+                                          pin["obs"], self.ep_return, 0, self._seed, 0, None)
         self._h2d, self._d2h = C.c_int64(), C.c_int64()
         self._call = (self.hp.L.dm_step_host, self.hp.h, C.byref(self._args), C.byref(self._h2d), C.byref(self._d2h))
         # objects handed out by earlier steps; one that nobody references any more is handed out again
@@ -264,8 +267,12 @@ class DPVecEnv:
             ep_ret, ep_len, reasons = self.ep_return[ids].copy(), self.ep_len[ids].copy(), self.reason[ids].copy()
             self.terminal_obs[ids] = self.obs[ids]
             self._counter += 1
-            self.hp.reset_host(n, self.idx, self.ep_len, self.clip, self.obs, mask=dones.view(np.uint8), qpos=self.qpos,
-                               qvel=self.qvel, ep_return=self.ep_return, seed=self._seed, counter=self._counter)
+            ra = self._rargs
+            ra.mask, ra.obs = self._args_ptr(dones), self._args_ptr(self.obs)
+            ra.seed, ra.counter = self._seed, self._counter
+            rc = self.hp.L.dm_reset_host(self.hp.h, C.byref(ra))
+            if rc:
+                N.check(rc, self.hp.h, "dm_reset_host")
             for k, i in enumerate(ids):
                 info = infos[i]
                 info["terminal_observation"] = self.terminal_obs[i].copy()
