@@ -68,6 +68,8 @@ struct dm_handle {
   int pdl = 1;                          // programmatic dependent launch of the tile kernel (DM_PDL=0 turns it off)
   int host_trace = 0;                   // DM_HOST_TRACE: print the mean host time of every phase of the mapped step at destroy
   double ht[5] = {0, 0, 0, 0, 0};       // copy-in, launch, wait, copy-out, calls
+  bool contact_slot_dirty = true, clip_slot_dirty = true;  // the pinned contact / clip slots may hold non-zero words
+  size_t slots_n = 0;                   // batch size the slots were last carved for (another n moves them)
   int host_chunk = 0;                   // environments per chunk of the mapped host step (0 = auto; DM_HOST_CHUNK)
   std::unique_ptr<CopyPool> pool;  // helper threads for the staging copies of big host batches (created on first use)
   bool pool_small = false;         // the pool was created for a small batch (no helper threads)
@@ -165,6 +167,9 @@ extern "C" int dm_create(int device, int robot, int env_kind, dm_handle** out) {
 extern "C" int dm_destroy(dm_handle* h) {
   if (!h) return DM_OK;
   cudaSetDevice(h->device);
+  // nothing may still be reading or writing the pinned blocks freed below
+  if (h->host_stream) cudaStreamSynchronize(h->host_stream);
+  if (h->host_stream2) cudaStreamSynchronize(h->host_stream2);
   cudaFree(h->d_rows);
   cudaFree(h->d_state_rows);
   cudaFree(h->d_stats);
@@ -683,8 +688,18 @@ static int step_host_mapped(dm_handle* h, const dm_step_args* a, const StepStage
                       {g.hz, nullptr, a->reason, 1}, {bt, nullptr, ct, sizeof(float) * d.nu},
                       {g.hm, nullptr, a->terms, sizeof(float) * DM_NTERMS}, {g.hi, nullptr, a->idx, 4}, {g.hl, nullptr, a->ep_len, 4},
                       {g.hk, nullptr, a->clip, 4}, {g.her, nullptr, a->ep_return, 4}};
+  // An absent contact / clip array reads as zeros.  The slot is zero-filled when it may hold something else (it was
+  // carved, or an earlier step put words there) and is then in place like any other array, so that a caller who has
+  // everything else in the pinned block keeps the single-launch path.
+  auto absent = [&](const void* src, void* slot, bool& dirty) {
+    if (src) { dirty = true; return; }
+    if (dirty) memset(slot, 0, 4 * n);
+    dirty = false;
+  };
+  absent(a->contact, g.hc, h->contact_slot_dirty);
+  absent(a->clip, g.hk, h->clip_slot_dirty);
   bool staged_any = false;
-  for (const Arr& x : ins) staged_any |= x.src != x.slot && !(x.slot == g.her && !x.src);
+  for (const Arr& x : ins) staged_any |= x.src && x.src != x.slot;
   for (const Arr& x : outs) staged_any |= x.dst && x.dst != x.slot;
   // chunks: whole tiles, at most 16 per step, at least 2048 environments each; one chunk when nothing is staged
   constexpr size_t kMaxChunks = 16, kTile = 128;
@@ -723,9 +738,9 @@ static int step_host_mapped(dm_handle* h, const dm_step_args* a, const StepStage
     const size_t e0 = c * chunk, e1 = e0 + chunk < n ? e0 + chunk : n, m = e1 - e0;
     CopyPool::Seg segs[CopyPool::kMaxSegs];
     int ns = 0;
-    for (const Arr& x : ins) {  // an absent contact / clip array reads as zeros; an absent ep_return is not read at all
-      if (x.src == x.slot || (x.slot == g.her && !x.src)) continue;
-      segs[ns++] = CopyPool::Seg{(char*)x.slot + e0 * x.row, x.src ? (const char*)x.src + e0 * x.row : nullptr, m * x.row};
+    for (const Arr& x : ins) {  // absent arrays: contact / clip slots are zero already, ep_return is not read at all
+      if (x.src == x.slot || !x.src) continue;
+      segs[ns++] = CopyPool::Seg{(char*)x.slot + e0 * x.row, (const char*)x.src + e0 * x.row, m * x.row};
     }
     pool->copy_many(segs, ns);
     lap(0);
@@ -773,6 +788,10 @@ extern "C" int dm_step_host(dm_handle* h, const dm_step_args* a, int64_t* h2d_by
   rc = ensure_stage(h, h->step_stage, step_stage_bytes(d, n));
   if (rc) return rc;
   const StepStage g = carve_step(h, n);
+  if (h->slots_n != n) {
+    h->slots_n = n;
+    h->contact_slot_dirty = h->clip_slot_dirty = true;
+  }
   cudaStream_t s = h->host_stream;
   // a buffer that already IS its staging slot (dm_host_buffers) needs no copy
   const bool small = sizeof(float) * n * (d.nq + d.nv + d.na) < 128 * 1024;  // never reaches the pool's parallel threshold

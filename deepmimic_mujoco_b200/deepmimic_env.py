@@ -23,9 +23,6 @@ class DPEnv:
     ENV_CFG = DPEnvConfig()
 
     def __init__(self, motion=None, load_mocap=True, robot="humanoid3d", _profile=False, device=0, physics=None):
-        if not load_mocap:
-            raise N.DmError("DPEnv(load_mocap=False) only exists for the reference loader's internal FK pass "
-                            "(mocap_v2.py:301-307); here that pass is the dm_fk_tables kernel")
         self.PROFILE = _profile
         self.motion_config = MotionConfig(motion=motion, robot=robot)
         self.robot_config = RobotConfig(robot=robot)
@@ -34,6 +31,14 @@ class DPEnv:
         self.mocap = self._vec.hp.mocaps[0]
         self.mocap_dt = self.mocap.dt
         self.mocap_data_len = self.mocap.get_length()
+        # load_mocap=False (deepmimic_env.py:276-291, the loader's internal FK env): no tables, mocap_data_len = 1 and
+        # step() returns (obs, 0, False, {}) before any reward / termination / counter logic (:394-395).  The kernel still
+        # needs a table to index, so the motion's clip stays loaded underneath; only this view hides it.
+        self._no_mocap = not load_mocap
+        if self._no_mocap:
+            self.mocap = SimpleNamespace(data_config=None, data_vel=None, data_body_xpos=None, data_geom_xpos=None, dt=None)
+            self.mocap_dt = None
+            self.mocap_data_len = 1
         self.action_space = self._vec.action_space
         self.observation_space = self._vec.observation_space
         self.sim = SimpleNamespace(data=SimpleNamespace(qpos=np.zeros(self.model.nq), qvel=np.zeros(self.model.nv), time=0.0))
@@ -54,18 +59,52 @@ class DPEnv:
         self.reset_model(idx_init)
 
     def reset(self):
+        self.episode_reward = 0  # deepmimic_env.py:496-500: only reset() zeroes the episode counters
+        self.episode_length = 0
+        self._vec.ep_len[0] = 0
+        self._vec.ep_return[0] = 0.0
         return self.reset_model()
 
     def reset_model(self, idx_init=None):
-        obs = self._vec.reset(frame=None if idx_init is None else [idx_init])
+        """reference_state_init + set_state + observation (deepmimic_env.py:502-510); the episode counters are left alone."""
+        v = self._vec
+        keep = (int(v.ep_len[0]), float(v.ep_return[0]))
+        if self._no_mocap:  # :504-505: the observation of the current state, idx_curr = idx_init
+            self.idx_init = self.idx_curr = 0 if idx_init is None else int(idx_init)
+            return self._obs_only()
+        obs = v.reset(frame=None if idx_init is None else [idx_init])
+        v.ep_len[0], v.ep_return[0] = keep
         self._pull()
         self.idx_init = self.idx_curr
         return obs[0].astype(np.float64)
+
+    def _obs_only(self, force_state=None):
+        """get_obs of the current (or given) state without touching reward, termination or counters."""
+        v = self._vec
+        keep = (int(v.idx[0]), int(v.ep_len[0]), float(v.ep_return[0]))
+        if force_state is not None:
+            v.qpos[0], v.qvel[0] = force_state[0], force_state[1]
+        v.idx[0] = 0  # phase = clip(idx_curr / 1, 0, 1) with idx_curr in {-1, 0} -> 0
+        contact = np.asarray([force_state[2]], dtype=np.uint32) if force_state is not None and len(force_state) > 2 else None
+        v.hp.step_host(1, v.qpos, v.qvel, np.zeros((1, v.hp.na), np.float32), contact, v.idx, v.ep_len, v.clip, v.obs,
+                       v.reward, v.done, v.reason, v.torque, v.terms, v.ep_return)
+        obs = v.obs[0].astype(np.float64)
+        ph = self.ENV_CFG.ADD_PHASE_OBS and v.hp.obs_dim - 1
+        if ph:
+            obs[ph] = 0.0
+        v.idx[0], v.ep_len[0], v.ep_return[0] = keep
+        self.sim.data.qpos = v.qpos[0].astype(np.float64)
+        self.sim.data.qvel = v.qvel[0].astype(np.float64)
+        return obs
 
     def step(self, action, force_state=None):
         a = np.asarray(action, dtype=np.float32)
         assert a.shape == (self._vec.hp.na,), "action must have %d entries" % self._vec.hp.na
         v = self._vec
+        if self._no_mocap:  # deepmimic_env.py:394-395
+            if force_state is None:
+                raise N.DmError("DPEnv.step needs force_state=(qpos, qvel): MuJoCo's mj_step is outside this package")
+            return self._obs_only(force_state), 0, False, {}
         fs = None
         if force_state is not None:
             fs = (np.asarray(force_state[0], dtype=np.float32)[None], np.asarray(force_state[1], dtype=np.float32)[None]) + \

@@ -17,13 +17,34 @@ Two data paths:
 """
 from __future__ import annotations
 
-import sys
 import ctypes as C
+import weakref
+from collections.abc import Sequence
 
 import numpy as np
 
 from . import _native as N
 from .hotpath import HotPath
+
+
+def _vecenv_base():
+    """stable_baselines3's VecEnv ABC when it is importable, else `object`.  SB3 wraps anything that is not an
+    `isinstance(env, VecEnv)` in a DummyVecEnv (the reference hands a SubprocVecEnv to PPO, src/sb3_ppo.py:275-278,307),
+    so the drop-in has to BE one."""
+    try:
+        from stable_baselines3.common.vec_env import VecEnv
+        return VecEnv
+    except Exception:
+        return object
+
+
+def _gym_box():
+    for mod in ("gymnasium", "gym"):
+        try:
+            return __import__(mod + ".spaces", fromlist=["Box"]).Box
+        except Exception:
+            pass
+    return None
 
 
 class Box:
@@ -49,44 +70,99 @@ class Box:
         return x.shape == self.shape and bool(np.all(x >= self.low) and np.all(x <= self.high))
 
 
-class LazyInfos(list):
-    """The `infos` list of a VecEnv step: a real list of num_envs per-env dicts whose entries are created on first
-    access.  Building num_envs empty dicts eagerly costs more than the whole GPU step at 4096 environments."""
+class LazyInfos(Sequence):
+    """The `infos` of a VecEnv step: a sequence of num_envs per-env dicts whose entries are created on first access.
+    (SB3's SubprocVecEnv returns a tuple here; consumers index, iterate and take len().)  Construction is O(1): building
+    num_envs empty dicts -- or even a list of num_envs None entries -- eagerly costs more than the whole GPU step at 4096
+    environments (17 us; 1.1 ms at 262144)."""
+
+    __slots__ = ("_n", "_d", "__weakref__")
 
     def __init__(self, n):
-        super().__init__([None] * n)
-        self._touched = []  # indices whose dict exists
+        self._n = int(n)
+        self._d = {}
+
+    def __len__(self):
+        return self._n
 
     def __getitem__(self, i):
-        v = list.__getitem__(self, i)
         if isinstance(i, slice):
-            return [self[j] for j in range(*i.indices(len(self)))]
+            return [self[j] for j in range(*i.indices(self._n))]
+        i = int(i)
+        if i < 0:
+            i += self._n
+        if not 0 <= i < self._n:
+            raise IndexError("info index out of range")
+        v = self._d.get(i)
         if v is None:
-            v = {}
-            list.__setitem__(self, i, v)
-            self._touched.append(i)
+            v = self._d[i] = {}
         return v
 
-    def _recycle(self):
-        """Back to n untouched entries (DPVecEnv hands a list out again once its previous holder has dropped it:
-        building n entries per step costs 17 us at 4096 environments and grows with n)."""
-        for i in self._touched:
-            list.__setitem__(self, i, None)
-        self._touched.clear()
-        return self
+    def __setitem__(self, i, v):
+        i = int(i)
+        if i < 0:
+            i += self._n
+        if not 0 <= i < self._n:
+            raise IndexError("info index out of range")
+        self._d[i] = v
 
     def __iter__(self):
-        for i in range(len(self)):
+        for i in range(self._n):
             yield self[i]
 
     def __eq__(self, other):
-        return list(iter(self)) == list(other)
+        try:
+            return len(other) == self._n and all(a == b for a, b in zip(self, other))
+        except TypeError:
+            return NotImplemented
+
+    __hash__ = None
+
+    def touched(self):
+        """Indices whose dict exists (every other entry is an empty dict)."""
+        return sorted(self._d)
 
 
-class DPVecEnv:
+class _OutputRing:
+    """Caller-owned output arrays without per-step allocation.  A ring slot is a block of (pinned) memory; every hand-out
+    wraps it in a NEW 1-D ndarray `f` (whose base is the slot's buffer object, not an ndarray) and gives the caller
+    `f.reshape(shape)`.  numpy collapses the base of every further view -- slices, reshapes, torch.from_numpy -- onto `f`,
+    so `f` dies exactly when nothing of the caller's aliases the slot any more; the ring keeps only a weak reference to it
+    and reuses a slot whose reference is dead.  When the caller holds every slot (SAC's replay buffer keeping observations,
+    a rollout buffer of views) a plain fresh array is handed out instead: never an array somebody may still read."""
+
+    def __init__(self, shape, dtype, slots, pinned):
+        self.shape, self.dtype = tuple(shape), np.dtype(dtype)
+        self._slots = []  # [buffer object, weakref to the live 1-D array or None]
+        self._keep = []
+        count = int(np.prod(self.shape))
+        for _ in range(slots):
+            if pinned:
+                import torch
+                t = torch.empty(max(count * self.dtype.itemsize, 1), dtype=torch.uint8, pin_memory=True)
+                self._keep.append(t)
+                buf = (C.c_uint8 * (count * self.dtype.itemsize)).from_address(t.data_ptr())
+            else:
+                buf = (C.c_uint8 * (count * self.dtype.itemsize))()
+            self._slots.append([buf, None])
+
+    def get(self):
+        for s in self._slots:
+            if s[1] is None or s[1]() is None:
+                f = np.frombuffer(s[0], self.dtype)
+                s[1] = weakref.ref(f)
+                return f.reshape(self.shape)
+        return np.empty(self.shape, self.dtype)
+
+
+class DPVecEnv(_vecenv_base()):
     def __init__(self, num_envs, motion="walk", robot="humanoid3d", combined=False, device=0, seed=0, physics=None,
-                 info_terms=False, copy_outputs=True, contact_from_fk=False):
+                 info_terms=False, copy_outputs=True, contact_from_fk=False, timelimit_truncated=False):
         self.num_envs = int(num_envs)
+        # The reference's envs end on MAX_EP_LENGTH inside step() as a plain `done` (deepmimic_env.py:435-438,
+        # combined_env.py:442-445): no gym TimeLimit wrapper, so SubprocVecEnv reports TimeLimit.truncated = False and SB3
+        # does not bootstrap the terminal value.  True is an opt-in deviation.
+        self.timelimit_truncated = bool(timelimit_truncated)
         self.robot = "unitree_g1" if combined else robot
         self.combined = bool(combined)
         self.device = device
@@ -105,8 +181,16 @@ class DPVecEnv:
         lo, hi = mc["ctrl_lo"][:d.na].copy(), mc["ctrl_hi"][:d.na].copy()
         if self.combined:  # combined_env.py:194-200: ctrlrange / ACT_SCALE
             lo, hi = lo / 20.0, hi / 20.0
-        self.action_space = Box(lo, hi)
-        self.observation_space = Box(np.full(d.obs_dim, -np.inf), np.full(d.obs_dim, np.inf))
+        GymBox = _gym_box()
+        if type(self).__mro__[1] is not object and GymBox is not None:  # a real SB3 VecEnv wants real gym spaces
+            act_space = GymBox(low=lo, high=hi, dtype=np.float32)
+            obs_space = GymBox(low=-np.inf, high=np.inf, shape=(d.obs_dim,), dtype=np.float32)
+        else:
+            act_space = Box(lo, hi)
+            obs_space = Box(np.full(d.obs_dim, -np.inf), np.full(d.obs_dim, np.inf))
+        if type(self).__mro__[1] is not object:
+            super().__init__(self.num_envs, obs_space, act_space)
+        self.action_space, self.observation_space = act_space, obs_space
         n = self.num_envs
         self._seed, self._counter = int(seed), 0
         self.copy_outputs = bool(copy_outputs)
@@ -138,37 +222,18 @@ class DPVecEnv:
                                           pin["obs"], self.ep_return, 0, self._seed, 0, None)
         self._h2d, self._d2h = C.c_int64(), C.c_int64()
         self._call = (self.hp.L.dm_step_host, self.hp.h, C.byref(self._args), C.byref(self._h2d), C.byref(self._d2h))
-        # objects handed out by earlier steps; one that nobody references any more is handed out again
-        self._rings = {"obs": [], "rew": [], "done": [], "infos": []}
-        self._makers = {"obs": self._new_obs_array, "rew": lambda: np.empty_like(pin["reward"]),
-                        "done": lambda: np.empty(n, np.bool_), "infos": lambda: LazyInfos(n)}
+        # caller-owned outputs (copy_outputs=True) come from small rings that are reused only once the caller has
+        # dropped every view of a slot (see _OutputRing).  The observation slots are PINNED host memory: dm_step_host
+        # then lets the kernel write the observations straight into the array the caller receives.
+        self._rings = {"obs": _OutputRing(pin["obs"].shape, np.float32, 4, True),
+                       "rew": _OutputRing((n,), np.float32, 4, False), "done": _OutputRing((n,), np.bool_, 4, False)}
 
     @staticmethod
     def _args_ptr(x):
         return x.__array_interface__["data"][0]
 
-    def _new_obs_array(self):
-        """A caller-owned observation array.  The ones that live in the reuse ring are PINNED host memory: dm_step_host
-        then lets the kernel write the observations straight into them (no copy out of the staging block).  Once the
-        ring is full (the caller keeps more than four steps of observations alive) further arrays are ordinary ones."""
-        shape = self._pin["obs"].shape
-        if len(self._rings["obs"]) < 4:
-            import torch
-            return torch.empty(shape, dtype=torch.float32, pin_memory=True).numpy()
-        return np.empty(shape, np.float32)
-
     def _fresh(self, kind):
-        """A caller-owned object for this step's observations / rewards / dones / infos.  Objects handed out earlier that
-        the caller has dropped (only the ring still references them) are reused: a fresh 1 MB array is a fresh mmap whose
-        pages fault in during the copy, which costs more than the copy itself, and a list of n entries costs O(n) to build."""
-        ring = self._rings[kind]
-        for a in ring:
-            if sys.getrefcount(a) == 3:  # the ring, the loop variable, getrefcount's argument
-                return a._recycle() if kind == "infos" else a
-        a = self._makers[kind]()
-        if len(ring) < 4:
-            ring.append(a)
-        return a
+        return self._rings[kind].get()
 
     def input_buffers(self):
         """The pinned (qpos, qvel, contact, action) arrays of the next step.  A simulator that writes its
@@ -180,7 +245,11 @@ class DPVecEnv:
     # ------------------------------------------------------------------ VecEnv surface
     def set_clips(self, clip_ids):
         """DPEnv semantics with several motions: which clip each env imitates."""
-        self.clip[:] = np.asarray(clip_ids, dtype=np.int32)
+        ids = np.asarray(clip_ids, dtype=np.int64)
+        n_clips = len(self.hp.clip_lens)
+        if ids.size and (ids.min() < 0 or ids.max() >= n_clips):  # the reference indexes a Python list: IndexError
+            raise IndexError("clip id out of range: this env has %d clip(s) %s" % (n_clips, self.motions))
+        self.clip[:] = ids.astype(np.int32)
 
     def seed(self, seed=None):
         self._seed = int(seed or 0)
@@ -189,12 +258,27 @@ class DPVecEnv:
     def reset(self, frame=None, coin=None, mask=None):
         """All envs (or those in `mask`): reference-state initialisation + reset observation."""
         self._counter += 1
-        self.hp.reset_host(self.num_envs, self.idx, self.ep_len, self.clip, self.obs,
+        if frame is not None:
+            frame = np.ascontiguousarray(frame, dtype=np.int32)
+            if not self.combined:  # data_config[idx_init] of the reference raises IndexError (deepmimic_env.py:506)
+                lens = np.asarray(self.hp.clip_lens, dtype=np.int64)[self.clip]
+                bad = (frame < -lens) | (frame >= lens)
+                if mask is not None:
+                    bad &= np.asarray(mask, dtype=bool)
+                if bad.any():
+                    raise IndexError("reset frame out of range for env %d (clip length %d)" % (int(np.nonzero(bad)[0][0]), int(lens[np.nonzero(bad)[0][0]])))
+                frame = np.where(frame < 0, frame + lens, frame).astype(np.int32)  # Python's negative indexing
+        # always into the handle's own pinned slot: an array handed to the caller by an earlier step() is never rewritten
+        obs = self._pin["obs"]
+        if mask is not None and self.obs is not obs:
+            np.copyto(obs, self.obs)
+        self.obs = obs
+        self.hp.reset_host(self.num_envs, self.idx, self.ep_len, self.clip, obs,
                            mask=None if mask is None else np.ascontiguousarray(mask, dtype=np.uint8),
-                           frame=None if frame is None else np.ascontiguousarray(frame, dtype=np.int32),
+                           frame=frame,
                            coin=None if coin is None else np.ascontiguousarray(coin, dtype=np.int32),
                            qpos=self.qpos, qvel=self.qvel, ep_return=self.ep_return, seed=self._seed, counter=self._counter)
-        return self.obs.copy()
+        return obs.copy()
 
     def step_async(self, actions, force_state=None):
         actions = np.asarray(actions)
@@ -218,11 +302,25 @@ class DPVecEnv:
         n = self.num_envs
         p = self._pin
         contact = None
+        failed = None
         if self._force is not None:
             fs = self._force
         elif self.physics is not None:
-            # the torque belongs to the kernel (gear * clip(scale * a, ctrlrange)), so physics gets the action
-            fs = self.physics(self.qpos, self.qvel, self._actions)
+            # the torque belongs to the kernel (gear * clip(scale * a, ctrlrange)), so physics gets the action.
+            # A simulation that diverges (deepmimic_env.py:359-378: any exception out of do_simulation) ends the episode
+            # with (obs * 0, 0, True, {}): the callback either raises -- every env of the batch failed -- or returns a
+            # fourth element, a per-env boolean mask of the environments whose simulation failed.
+            try:
+                fs = self.physics(self.qpos, self.qvel, self._actions)
+            except Exception as exc:  # noqa: BLE001  (the reference catches everything)
+                print("Error in step: physics callback raised %r; all %d episodes end" % (exc, n))
+                fs, failed = (self.qpos, self.qvel, None), np.ones(n, np.bool_)
+            if len(fs) > 3 and fs[3] is not None and np.any(fs[3]):
+                failed = np.asarray(fs[3], dtype=np.bool_)
+                # failed rows keep their last valid state so the kernel sees finite numbers; their outputs are overwritten below
+                q, v = np.array(fs[0], dtype=np.float32), np.array(fs[1], dtype=np.float32)
+                q[failed], v[failed] = self.qpos[failed], self.qvel[failed]
+                fs = (q, v, fs[2])
         else:
             raise N.DmError("DPVecEnv.step needs force_state=(qpos, qvel[, contact]) or a physics callback: MuJoCo's "
                             "mj_step is outside this package")
@@ -247,8 +345,13 @@ class DPVecEnv:
             N.check(rc, h, "dm_step_host")
         self.qpos, self.qvel, self._actions = p["qpos"], p["qvel"], p["action"]  # the pinned copies, never the caller's arrays
         self.h2d_bytes, self.d2h_bytes = self._h2d.value, self._d2h.value
+        if failed is not None:  # (obs * 0, 0, True, {}) and no counter advanced past the failure (deepmimic_env.py:377-378)
+            self.obs[failed] = 0.0
+            self.reward[failed] = 0.0
+            self.done[failed] = 1
+            self.reason[failed] = 8
         dones = self.done.view(np.bool_)
-        infos = self._fresh("infos")
+        infos = LazyInfos(n)
         if self.info_terms:
             for i in range(n):
                 if self.reason[i] != 8:
@@ -276,7 +379,7 @@ class DPVecEnv:
             for k, i in enumerate(ids):
                 info = infos[i]
                 info["terminal_observation"] = self.terminal_obs[i].copy()
-                info["TimeLimit.truncated"] = bool(reasons[k] == 5)
+                info["TimeLimit.truncated"] = bool(self.timelimit_truncated and reasons[k] == 5)
                 if reasons[k] not in (0, 8):
                     info["done_reason"] = N.DONE_REASONS[reasons[k]]
                 info["episode"] = {"r": float(ep_ret[k]), "l": int(ep_len[k])}

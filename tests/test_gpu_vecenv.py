@@ -38,7 +38,7 @@ def test_vecenv_matches_oracle_with_autoreset():
         contact = rng.integers(0, 4, n).astype(np.uint32)
         act = rng.uniform(-2, 2, (n, 28)).astype(np.float32)
         obs, rew, done, infos = env.step(act, force_state=(q, v, contact))
-        assert isinstance(infos, list) and isinstance(infos, LazyInfos) and len(infos) == n
+        assert isinstance(infos, LazyInfos) and len(infos) == n
         assert obs.dtype == np.float32 and done.dtype == np.bool_
         for i, o in enumerate(ors):
             wo, wr, wd, wi = o.step(act[i].astype(np.float64), (q[i].astype(np.float64), v[i].astype(np.float64)), int(contact[i]))
@@ -195,4 +195,113 @@ def test_combined_env_single_env_mirror():
         np.testing.assert_allclose(got[0], want[0], rtol=RTOL, atol=ATOL)
         np.testing.assert_allclose(got[1], want[1], rtol=RTOL, atol=ATOL)
         assert got[2] == want[2] and env.current_motion_n_steps == o.current_motion_n_steps
+    env.close()
+
+
+def test_outputs_held_by_the_caller_never_change():
+    """SAC keeps _last_obs, rollout buffers keep views; arrays handed out by step() must stay the caller's."""
+    from deepmimic_mujoco_b200.vec_env import DPVecEnv
+    from oracle.envs import SingleClipEnv
+    n = 256
+    rng = np.random.default_rng(3)
+    env = DPVecEnv(n, motion="walk", robot="humanoid3d", seed=1)
+    env.reset()
+    o = SingleClipEnv("walk", "humanoid3d")
+    held = []
+    for t in range(9):
+        q, v = _states(o, rng, n)
+        out = env.step(rng.uniform(-1, 1, (n, 28)).astype(np.float32), force_state=(q, v))
+        keep = (out[0][::2], out[1].reshape(-1, 1), out[2])  # views, not the arrays themselves
+        held.append((keep, [x.copy() for x in keep]))
+        del out
+        if t % 3 == 2:
+            env.reset(mask=np.arange(n) % 2 == 0)  # a masked reset must not touch arrays already handed out
+        for views, copies in held:
+            for a, b in zip(views, copies):
+                np.testing.assert_array_equal(a, b)
+    env.close()
+
+
+def test_time_limit_is_a_plain_done_like_the_reference():
+    """deepmimic_env.py:435-438: MAX_EP_LENGTH ends the episode inside step(); no TimeLimit wrapper, so SB3 must not see
+    TimeLimit.truncated = True (it would bootstrap the terminal value)."""
+    from deepmimic_mujoco_b200.vec_env import DPVecEnv
+    from oracle.envs import SingleClipEnv
+    o = SingleClipEnv("walk", "humanoid3d")
+    for flag in (False, True):
+        env = DPVecEnv(4, motion="walk", robot="humanoid3d", seed=1, timelimit_truncated=flag)
+        env.reset(frame=np.zeros(4, np.int32))
+        env.ep_len[:] = [1000, 5, 1000, 999]
+        q = np.repeat(np.asarray(o.mocap.data_config[0], np.float32)[None], 4, 0)
+        v = np.repeat(np.asarray(o.mocap.data_vel[0], np.float32)[None], 4, 0)
+        obs, rew, done, infos = env.step(np.zeros((4, 28), np.float32), force_state=(q, v))
+        assert done.tolist() == [True, False, True, False]
+        for i in (0, 2):
+            assert infos[i]["done_reason"] == "max_ep_len" and infos[i]["TimeLimit.truncated"] is flag
+        env.close()
+
+
+def test_failing_physics_ends_the_episode_like_a_diverged_simulation():
+    """deepmimic_env.py:359-378: an exception out of do_simulation returns (obs * 0, 0, True, {})."""
+    from deepmimic_mujoco_b200.vec_env import DPVecEnv
+    n = 8
+    state = {"mode": "ok"}
+
+    def physics(qpos, qvel, action):
+        if state["mode"] == "raise":
+            raise FloatingPointError("mjWARN_BADQACC")
+        bad = np.zeros(n, bool)
+        q, v = qpos.copy(), qvel.copy()
+        if state["mode"] == "mask":
+            bad[[1, 6]] = True
+            q[bad] = np.nan
+        return q, v, None, bad
+
+    env = DPVecEnv(n, motion="walk", robot="humanoid3d", seed=2, physics=physics)
+    env.reset()
+    obs, rew, done, infos = env.step(np.zeros((n, 28), np.float32))
+    assert not done.any()
+    state["mode"] = "mask"
+    obs, rew, done, infos = env.step(np.zeros((n, 28), np.float32))
+    assert done.tolist() == [i in (1, 6) for i in range(n)]
+    for i in (1, 6):
+        assert rew[i] == 0 and not infos[i]["terminal_observation"].any() and "done_reason" not in infos[i]
+        assert env.ep_len[i] == 0  # auto-reset like any finished episode
+    assert np.isfinite(obs).all()
+    state["mode"] = "raise"
+    obs, rew, done, infos = env.step(np.zeros((n, 28), np.float32))
+    assert done.all() and not rew.any()
+    env.close()
+
+
+def test_clip_ids_and_reset_frames_are_validated_on_the_host():
+    """an id / frame outside the table was a silent out-of-bounds read; the reference raises IndexError."""
+    from deepmimic_mujoco_b200.vec_env import DPVecEnv
+    env = DPVecEnv(4, motion=["spinkick", "dance_b"], robot="humanoid3d")
+    env.set_clips([0, 1, 1, 0])
+    with pytest.raises(IndexError):
+        env.set_clips([0, 2, 0, 0])
+    with pytest.raises(IndexError):
+        env.set_clips([0, -1, 0, 0])
+    env.reset(frame=[77, 152, 0, -1])  # last frames of both clips; -1 is Python's last element
+    assert env.idx.tolist() == [77, 152, 0, 77]
+    with pytest.raises(IndexError):
+        env.reset(frame=[78, 0, 0, 0])
+    env.close()
+
+
+def test_dpenv_without_mocap_returns_the_observation_only():
+    """deepmimic_env.py:276-291,394-395: DPEnv(load_mocap=False).step -> (obs, 0, False, {}) and no counter moves."""
+    from deepmimic_mujoco_b200 import DPEnv
+    from oracle.envs import SingleClipEnv
+    o = SingleClipEnv("walk", "humanoid3d")
+    env = DPEnv(motion="walk", load_mocap=False)
+    assert env.mocap.data_config is None and env.mocap_data_len == 1
+    q, v = np.asarray(o.mocap.data_config[9], np.float32), np.asarray(o.mocap.data_vel[9], np.float32)
+    o.reset(0)
+    want = o.step(np.zeros(28), (q.astype(np.float64), v.astype(np.float64)))[0]
+    got = env.step(np.zeros(28), force_state=(q, v))
+    assert got[1:] == (0, False, {})
+    np.testing.assert_allclose(got[0][:-1], want[:-1], rtol=RTOL, atol=ATOL)
+    assert got[0][-1] == 0.0 and env.episode_length == 1 and env.idx_curr == 0
     env.close()
