@@ -88,41 +88,30 @@ struct StepOut {
 };
 
 // ---- observation (get_obs) -----------------------------------------------------------------
-// Writes the DIM observation values through io.obs(j, v) and returns max / min with numpy's
-// NaN-propagating semantics for the bounds guard.
+// The entries behind the two joint blocks: torso (deepmimic_env.py:47-76), contacts (:78-121), phase (:139-143),
+// player action (:145-173).  torso roll / pitch / yaw, cvel = [angular; linear] of the torso body.  mx / mn carry the
+// running max / min of the observation (numpy's NaN-propagating semantics) for the bounds guard.
 template <int KIND, class Rb, class IO>
-DM_HD void write_obs(IO& io, const FkOut<float>& fk, const float* root_rpy, uint32_t contact, int frame, int len,
-                     int clip, float& omax, float& omin) {
+DM_HD void write_obs_tail(IO& io, float roll, float pitch, float yaw, const float* cvel, uint32_t contact, int frame, int len,
+                          int clip, float& mx, float& mn) {
   using L = ObsLayout<KIND, Rb>;
-  float mx = -INFINITY, mn = INFINITY;
   auto put = [&](int j, float v) {
     io.obs(j, v);
     mx = dm_max_nan(mx, v);
     mn = dm_min_nan(mn, v);
   };
-#pragma unroll
-  for (int j = 0; j < Rb::NJ; ++j) put(j, io.qpos(7 + j));
-#pragma unroll
-  for (int j = 0; j < Rb::NJ; ++j) put(Rb::NJ + j, io.qvel(6 + j) * 0.1f);
-  // torso block (deepmimic_env.py:47-76): rpy of the torso quaternion, yaw-aligned linear velocity
-  float roll, pitch, yaw;
-  if (Rb::kTorsoIsRoot) {  // torso body carries the free joint: its xquat is the normalised qpos[3:7]
-    roll = root_rpy[0]; pitch = root_rpy[1]; yaw = root_rpy[2];
-  } else {
-    dm_rpy(fk.tq[0], fk.tq[1], fk.tq[2], fk.tq[3], roll, pitch, yaw);
-  }
   float sy, cy;
   dm_sincos_f(-yaw, sy, cy);
-  const float vx = cy * fk.cvel[3] - sy * fk.cvel[4];
-  const float vy = sy * fk.cvel[3] + cy * fk.cvel[4];
+  const float vx = cy * cvel[3] - sy * cvel[4];
+  const float vy = sy * cvel[3] + cy * cvel[4];
   put(L::TORSO + 0, roll * 0.1f);
   put(L::TORSO + 1, pitch * 0.1f);
   put(L::TORSO + 2, vx * 0.1f);
   put(L::TORSO + 3, vy * 0.1f);
-  put(L::TORSO + 4, fk.cvel[5] * 0.1f);
-  put(L::TORSO + 5, fk.cvel[0] * 0.1f);
-  put(L::TORSO + 6, fk.cvel[1] * 0.1f);
-  put(L::TORSO + 7, fk.cvel[2] * 0.1f);
+  put(L::TORSO + 4, cvel[5] * 0.1f);
+  put(L::TORSO + 5, cvel[0] * 0.1f);
+  put(L::TORSO + 6, cvel[1] * 0.1f);
+  put(L::TORSO + 7, cvel[2] * 0.1f);
   if (KIND == KIND_SINGLE) {  // [rfoot & floor, lfoot & floor] (:78-105)
     put(L::CONTACT + 0, (contact & 1u) ? 1.0f : 0.0f);
     put(L::CONTACT + 1, (contact & 2u) ? 1.0f : 0.0f);
@@ -142,6 +131,30 @@ DM_HD void write_obs(IO& io, const FkOut<float>& fk, const float* root_rpy, uint
     put(L::PA + 5, clip == C_TO_GETUP ? 1.0f : 0.0f);  // pa_getup_state (combined_env.py:499-504)
     put(L::PA + 6, clip == C_GETUP ? 1.0f : 0.0f);
   }
+}
+
+// Writes the DIM observation values through io.obs(j, v) and returns max / min with numpy's
+// NaN-propagating semantics for the bounds guard.
+template <int KIND, class Rb, class IO>
+DM_HD void write_obs(IO& io, const FkOut<float>& fk, const float* root_rpy, uint32_t contact, int frame, int len,
+                     int clip, float& omax, float& omin) {
+  float mx = -INFINITY, mn = INFINITY;
+  auto put = [&](int j, float v) {
+    io.obs(j, v);
+    mx = dm_max_nan(mx, v);
+    mn = dm_min_nan(mn, v);
+  };
+#pragma unroll
+  for (int j = 0; j < Rb::NJ; ++j) put(j, io.qpos(7 + j));
+#pragma unroll
+  for (int j = 0; j < Rb::NJ; ++j) put(Rb::NJ + j, io.qvel(6 + j) * 0.1f);
+  float roll, pitch, yaw;
+  if (Rb::kTorsoIsRoot) {  // torso body carries the free joint: its xquat is the normalised qpos[3:7]
+    roll = root_rpy[0]; pitch = root_rpy[1]; yaw = root_rpy[2];
+  } else {
+    dm_rpy(fk.tq[0], fk.tq[1], fk.tq[2], fk.tq[3], roll, pitch, yaw);
+  }
+  write_obs_tail<KIND, Rb>(io, roll, pitch, yaw, fk.cvel, contact, frame, len, clip, mx, mn);
   omax = mx;
   omin = mn;
 }
@@ -191,6 +204,35 @@ struct EeSink {
   }
 };
 
+// The reward once the per-joint sums exist (deepmimic_env.py:213-256): `tail` = the frame's row from RowLayout::ROLL on
+// (roll*, pitch*, ee*[12], com*[3], vxy*[2]).  Shared by the thread-per-environment step and the team kernel's combine.
+template <class Rb, bool WANT_COM>
+DM_HD float reward_terms(float e_q, float e_v, float max_dq, int nlim, float e_ee, float roll, float pitch,
+                         const float* __restrict__ tail, const float* com_xpos, StepOut& so, RewardMid& mid) {
+  mid.vx_ref = tail[17];
+  mid.vy_ref = tail[18];
+  mid.sum_dq = e_q;
+  mid.max_dq = max_dq;
+  mid.d_roll = fabsf(roll - tail[0]);
+  mid.d_pitch = fabsf(pitch - tail[1]);
+  const float r_pose = expf(-(e_q + mid.d_pitch));
+  const float r_vel = expf(-0.1f * e_v);
+  const float r_ee = expf(-40.0f * e_ee);
+  float r_com = 0.0f;
+  if (WANT_COM) {
+    const float dx = tail[14] - com_xpos[0], dy = tail[15] - com_xpos[1], dz = tail[16] - com_xpos[2];
+    r_com = expf(-10.0f * (dx * dx + dy * dy + dz * dz));
+  }
+  const float qlim = float(nlim) / float(Rb::NSEL);
+  so.terms[0] = r_pose;
+  so.terms[1] = r_vel;
+  so.terms[2] = r_ee;
+  so.terms[3] = r_com;
+  so.terms[4] = qlim;
+  // wp 0.75, wv 0.1, we 0.15, wc 0.0, wj -0.1 (deepmimic_env.py:400-404); the wc term is exactly 0
+  return 0.75f * r_pose + 0.1f * r_vel + 0.15f * r_ee + (-0.1f) * qlim;
+}
+
 template <class Rb, class IO, bool WANT_COM>
 DM_HD float imitation_reward(const IO& io, const FkOut<float>& fk, const float* root_rpy, float e_ee,
                              const float* __restrict__ row, StepOut& so, RewardMid& mid) {
@@ -216,30 +258,7 @@ DM_HD float imitation_reward(const IO& io, const FkOut<float>& fk, const float* 
   Vec4 tail[5];  // roll*, pitch*, ee*[12], com*[3], vxy*[2], pad
 #pragma unroll
   for (int c = 0; c < 5; ++c) tail[c] = ld4(row + RL::ROLL + 4 * c);
-  auto T = [&](int i) { return tail[i >> 2].v[i & 3]; };
-  const float roll = root_rpy[0], pitch = root_rpy[1];
-  mid.vx_ref = T(17);
-  mid.vy_ref = T(18);
-  mid.sum_dq = e_q;
-  mid.max_dq = mx;
-  mid.d_roll = fabsf(roll - T(0));
-  mid.d_pitch = fabsf(pitch - T(1));
-  const float r_pose = expf(-(e_q + mid.d_pitch));
-  const float r_vel = expf(-0.1f * e_v);
-  const float r_ee = expf(-40.0f * e_ee);
-  float r_com = 0.0f;
-  if (WANT_COM) {
-    const float dx = T(14) - fk.com_xpos[0], dy = T(15) - fk.com_xpos[1], dz = T(16) - fk.com_xpos[2];
-    r_com = expf(-10.0f * (dx * dx + dy * dy + dz * dz));
-  }
-  const float qlim = float(nlim) / float(Rb::NSEL);
-  so.terms[0] = r_pose;
-  so.terms[1] = r_vel;
-  so.terms[2] = r_ee;
-  so.terms[3] = r_com;
-  so.terms[4] = qlim;
-  // wp 0.75, wv 0.1, we 0.15, wc 0.0, wj -0.1 (deepmimic_env.py:400-404); the wc term is exactly 0
-  return 0.75f * r_pose + 0.1f * r_vel + 0.15f * r_ee + (-0.1f) * qlim;
+  return reward_terms<Rb, WANT_COM>(e_q, e_v, mx, nlim, e_ee, root_rpy[0], root_rpy[1], &tail[0].v[0], fk.com_xpos, so, mid);
 }
 
 // accessors that emit the observation themselves (the warp kernel assembles it in shared memory) declare
@@ -249,33 +268,13 @@ struct io_zeroes_on_guard : std::true_type {};
 template <class IO>
 struct io_zeroes_on_guard<IO, std::enable_if_t<!IO::kZeroOnGuard>> : std::false_type {};
 
-// ---- one environment step --------------------------------------------------------------------
-// ROW_GIVEN: `rows` already points at THIS environment's packed row (the tile kernel staged it in shared memory)
-template <int KIND, class Rb, class IO, bool WANT_TERMS, bool ROW_GIVEN = false>
-DM_HD void env_step(IO& io, const ClipSet& cs, const float* __restrict__ rows, EnvState& st, uint32_t contact, StepOut& so) {
-  using RL = RowLayout<Rb>;
+// ---- everything after the reward sums: task reward, termination, motion state machine, counters ------------------
+// DPEnv.step (deepmimic_env.py:418-455) / DPCombinedEnv.step (combined_env.py:326-462); `z` = z of the mass-weighted
+// xipos COM, qv0 / qv1 = root linear velocity (qvel[0:2]).  Shared by the thread-per-environment step and the team kernel.
+template <int KIND, class Rb>
+DM_HD void step_logic(const ClipDesc& cd, int frame, int clip0, float imit, const RewardMid& mid, float z, float qv0, float qv1,
+                      EnvState& st, StepOut& so) {
   using OL = ObsLayout<KIND, Rb>;
-  const int clip0 = st.clip;
-  const ClipDesc cd = cs.clip[clip0];
-  const int frame = (KIND == KIND_SINGLE) ? st.idx : (st.idx % cd.len);
-  const int row_i = cd.row0 + (cd.fixed_row >= 0 ? cd.fixed_row : frame);
-  const float* __restrict__ row = ROW_GIVEN ? rows : rows + size_t(row_i) * RL::STRIDE;
-
-  write_torque<Rb>(io);
-
-  FkOut<float> fk;
-  EeSink<Rb> sink{row + RL::EE, 0.0f, cs.contact_from_fk != 0};
-  Rb::template fk<float>(io, fk, sink);
-
-  if (cs.contact_from_fk) contact = fk.contact;
-  float root_rpy[3];
-  dm_rpy_raw(io.qpos(3), io.qpos(4), io.qpos(5), io.qpos(6), root_rpy[0], root_rpy[1], root_rpy[2]);
-  float omax, omin;
-  write_obs<KIND, Rb>(io, fk, root_rpy, contact, frame, cd.len, clip0, omax, omin);
-
-  RewardMid mid;
-  const float imit = imitation_reward<Rb, IO, WANT_TERMS>(io, fk, root_rpy, sink.e2, row, so, mid);
-  const float z = fk.com[2];
   so.terms[7] = z;
   bool done = false;
   int reason = R_NONE;
@@ -301,7 +300,7 @@ DM_HD void env_step(IO& io, const ClipSet& cs, const float* __restrict__ rows, E
   } else {
     float task = 0.0f, im = imit;
     if (clip0 == C_WALK || clip0 == C_RUN) {  // combined_env.py:340-347
-      const float dx = mid.vx_ref - io.qvel(0), dy = mid.vy_ref - io.qvel(1);
+      const float dx = mid.vx_ref - qv0, dy = mid.vy_ref - qv1;
       task = expf(-10.0f * sqrtf(dx * dx + dy * dy));
     }
     if (clip0 == C_TO_GETUP) {  // :348-352
@@ -336,6 +335,35 @@ DM_HD void env_step(IO& io, const ClipSet& cs, const float* __restrict__ rows, E
   so.raw_reward = reward;
   so.done = done ? 1 : 0;
   so.reason = uint8_t(reason);
+}
+
+// ---- one environment step --------------------------------------------------------------------
+// ROW_GIVEN: `rows` already points at THIS environment's packed row (the tile kernel staged it in shared memory)
+template <int KIND, class Rb, class IO, bool WANT_TERMS, bool ROW_GIVEN = false>
+DM_HD void env_step(IO& io, const ClipSet& cs, const float* __restrict__ rows, EnvState& st, uint32_t contact, StepOut& so) {
+  using RL = RowLayout<Rb>;
+  using OL = ObsLayout<KIND, Rb>;
+  const int clip0 = st.clip;
+  const ClipDesc cd = cs.clip[clip0];
+  const int frame = (KIND == KIND_SINGLE) ? st.idx : (st.idx % cd.len);
+  const int row_i = cd.row0 + (cd.fixed_row >= 0 ? cd.fixed_row : frame);
+  const float* __restrict__ row = ROW_GIVEN ? rows : rows + size_t(row_i) * RL::STRIDE;
+
+  write_torque<Rb>(io);
+
+  FkOut<float> fk;
+  EeSink<Rb> sink{row + RL::EE, 0.0f, cs.contact_from_fk != 0};
+  Rb::template fk<float>(io, fk, sink);
+
+  if (cs.contact_from_fk) contact = fk.contact;
+  float root_rpy[3];
+  dm_rpy_raw(io.qpos(3), io.qpos(4), io.qpos(5), io.qpos(6), root_rpy[0], root_rpy[1], root_rpy[2]);
+  float omax, omin;
+  write_obs<KIND, Rb>(io, fk, root_rpy, contact, frame, cd.len, clip0, omax, omin);
+
+  RewardMid mid;
+  const float imit = imitation_reward<Rb, IO, WANT_TERMS>(io, fk, root_rpy, sink.e2, row, so, mid);
+  step_logic<KIND, Rb>(cd, frame, clip0, imit, mid, fk.com[2], io.qvel(0), io.qvel(1), st, so);
   // observation bounds guard (deepmimic_env.py:465-476, combined_env.py:474-485): zero observation,
   // zero reward, done, empty info -- evaluated after the counters advanced
   if (omax > 100.0f || omin < -100.0f) {

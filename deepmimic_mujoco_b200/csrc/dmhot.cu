@@ -13,6 +13,7 @@
 #include "../../include/dmhot.h"
 #include "dm_kernels.cuh"
 #include "dm_tile_launch.cuh"
+#include "dm_team_launch.cuh"
 #include "dm_pack.h"
 #include <chrono>
 #include "dm_copy_pool.h"
@@ -76,7 +77,9 @@ struct dm_handle {
   int copy_threads = -1;           // -1 = auto (3 helpers when the machine has the cores), DM_COPY_THREADS overrides
   // bookkeeping
   long long launches = 0;
-  int variant = -1;  // -1 auto
+  int variant = -1;  // -1 auto (team kernel), 0 strided only, 1 tile kernel (K1b), 2 team kernel (K1c)
+  unsigned long long* d_team_trace = nullptr;  // DM_TEAM_TRACE: device buffer [32] of %globaltimer marks (printed at destroy)
+  int team_maxt = 0, team_nin = 0, team_teams = 0, team_table = -1;  // tuning knobs of the team kernel (DM_TEAM_*; 0 / -1 = auto)
   int contact_mode = 0;  // DM_CONTACT_*
   int table_smem_override = -1, max_groups_override = 0, nbuf_override = 0, skip_compute = 0;  // tuning knobs (DM_TABLE_SMEM, DM_MAX_GROUPS)
   bool timing = false;
@@ -144,6 +147,15 @@ extern "C" int dm_create(int device, int robot, int env_kind, dm_handle** out) {
   if (const char* e = getenv("DM_PDL")) h->pdl = atoi(e);
   if (const char* e = getenv("DM_WIDE")) h->wide_override = atoi(e);
   if (const char* e = getenv("DM_ROW_STAGE")) h->row_stage_override = atoi(e);
+  if (const char* e = getenv("DM_VARIANT")) h->variant = atoi(e);
+  if (const char* e = getenv("DM_TEAM_MAXT")) h->team_maxt = atoi(e);
+  if (const char* e = getenv("DM_TEAM_NIN")) h->team_nin = atoi(e);
+  if (const char* e = getenv("DM_TEAM_TEAMS")) h->team_teams = atoi(e);
+  if (const char* e = getenv("DM_TEAM_TABLE")) h->team_table = atoi(e);
+  if (getenv("DM_TEAM_TRACE")) {
+    cudaMalloc(&h->d_team_trace, 32 * sizeof(unsigned long long));
+    cudaMemset(h->d_team_trace, 0, 32 * sizeof(unsigned long long));
+  }
   dispatch(h, [&](auto rb, auto kind) -> int {
     using Rb = decltype(rb);
     using OL = ObsLayout<decltype(kind)::value, Rb>;
@@ -167,6 +179,17 @@ extern "C" int dm_create(int device, int robot, int env_kind, dm_handle** out) {
 extern "C" int dm_destroy(dm_handle* h) {
   if (!h) return DM_OK;
   cudaSetDevice(h->device);
+  if (h->d_team_trace) {
+    unsigned long long t[32];
+    cudaDeviceSynchronize();
+    cudaMemcpy(t, h->d_team_trace, sizeof t, cudaMemcpyDeviceToHost);
+    const char* nm[10] = {"start", "dep-wait done", "tile+table landed", "part done", "barrier A", "combine done", "stats done",
+                          "loop end", "store read", "end"};
+    for (int w = 0; w < 2; ++w)
+      for (int k = 1; k < 10; ++k)
+        if (t[w * 16 + k]) fprintf(stderr, "[dmhot] team trace warp %d  %-18s +%6.2f us\n", w, nm[k], (double)(t[w * 16 + k] - t[0]) * 1e-3);
+    cudaFree(h->d_team_trace);
+  }
   // nothing may still be reading or writing the pinned blocks freed below
   if (h->host_stream) cudaStreamSynchronize(h->host_stream);
   if (h->host_stream2) cudaStreamSynchronize(h->host_stream2);
@@ -434,9 +457,53 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
                            reinterpret_cast<uintptr_t>(a->obs) | reinterpret_cast<uintptr_t>(a->action) |
                            reinterpret_cast<uintptr_t>(a->torque)) & 15u) == 0;
     int tiled = 0;
-    if (p.aos && h->variant != 0 && aligned && a->n >= TC::TE) tiled = a->n / TC::TE * TC::TE;
-    timing_begin(h, s);
-    if (tiled) {
+    const bool team = h->variant < 0 || h->variant == 2;
+    if (p.aos && team && aligned && a->n >= 32) {
+      // K1c: tiles of 32 environments, one team of four warps per tile (dm_team_kernel.cuh)
+      using MC = TeamCfg<KIND, Rb>;
+      tiled = a->n / MC::TE * MC::TE;
+      const int n_tiles = tiled / MC::TE;
+      const size_t table_bytes = sizeof(float) * (size_t)h->total_rows * RowLayout<Rb>::STRIDE;
+      const size_t avail = MC::SMEM_BUDGET - MC::FIXED_BYTES;
+      const int want = (n_tiles + h->num_sms - 1) / h->num_sms;  // teams per CTA that cover the batch in one wave
+      // instantiation by register budget: up to 4 teams per CTA get 128 registers, up to 6 get 80, 8 get 64
+      int maxt = want <= kTeamMaxtWide ? kTeamMaxtWide : want <= kTeamMaxtMid ? kTeamMaxtMid : kTeamMaxtFull;
+      if (a->terms) maxt = kTeamMaxtFull;
+      if (h->team_maxt > 0) maxt = h->team_maxt;
+      auto fit = [&](bool table, int nin) {  // teams that fit beside the table with nin input slots each
+        if (table && table_bytes > avail) return 0;
+        return (int)((avail - (table ? table_bytes : 0)) / (sizeof(float) * MC::team_floats(nin)));
+      };
+      int T = want < maxt ? (want < 1 ? 1 : want) : maxt;
+      if (h->team_teams > 0 && h->team_teams < T) T = h->team_teams;
+      // the clip table goes to shared memory when that does not cost a team; a second input slot when it costs neither
+      bool table_smem = fit(true, 1) >= T;
+      if (h->team_table >= 0) table_smem = h->team_table != 0 && fit(true, 1) >= 1;
+      if (fit(table_smem, 1) < T) T = fit(table_smem, 1);
+      const int tiles_per_team = (n_tiles + h->num_sms * T - 1) / (h->num_sms * T);
+      int nin = (tiles_per_team >= 2 && fit(table_smem, 2) >= T) ? 2 : 1;
+      if (h->team_nin > 0 && fit(table_smem, h->team_nin) >= T) nin = h->team_nin;
+      const int grid = (n_tiles + T - 1) / T < h->num_sms ? (n_tiles + T - 1) / T : h->num_sms;
+      const size_t smem = MC::FIXED_BYTES + (table_smem ? table_bytes : 0) + (size_t)T * sizeof(float) * MC::team_floats(nin);
+      StepParams q = p;
+      q.n = tiled;
+      TeamExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float)), nin, h->skip_compute,
+                   h->d_team_trace};
+      if (h->d_team_trace && h->launches % 64 == 0)
+        fprintf(stderr, "[dmhot] team launch: n_tiles %d grid %d teams %d maxt %d nin %d table_smem %d smem %zu\n", n_tiles, grid, T, maxt,
+                nin, (int)table_smem, smem);
+      TeamLaunch tl{grid, T, maxt, smem, s, h->pdl != 0, a->terms != nullptr, a->accumulate_stats != 0, table_smem};
+      timing_begin(h, s);
+      cudaError_t e = launch_team<KIND, Rb>(tl, q, ex);
+      CU(h, e);
+      h->launches++;
+    } else if (p.aos && h->variant == 1 && aligned && a->n >= TC::TE) {
+      tiled = a->n / TC::TE * TC::TE;
+      timing_begin(h, s);
+    } else {
+      timing_begin(h, s);
+    }
+    if (tiled && !team) {
       StepParams q = p;
       q.n = tiled;
       constexpr int GMAX = KernelGroups<Rb>::G;

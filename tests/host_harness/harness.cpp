@@ -7,6 +7,9 @@
 #include "../../deepmimic_mujoco_b200/csrc/dm_pack.h"
 #include "../../deepmimic_mujoco_b200/csrc/generated/robot_humanoid3d.cuh"
 #include "../../deepmimic_mujoco_b200/csrc/generated/robot_unitree_g1.cuh"
+#include "../../deepmimic_mujoco_b200/csrc/dm_team_core.cuh"
+#include "../../deepmimic_mujoco_b200/csrc/generated/parts_humanoid3d.cuh"
+#include "../../deepmimic_mujoco_b200/csrc/generated/parts_unitree_g1.cuh"
 
 using namespace dm;
 
@@ -35,6 +38,8 @@ struct DSink {
 
 static int g_contact_from_fk = 0;
 extern "C" void hh_set_contact_mode(int from_fk) { g_contact_from_fk = from_fk; }
+static int g_team = 0;  // 1: the team kernel's arithmetic (dm_team_core.cuh + generated parts), its four parts run in turn
+extern "C" void hh_set_team(int on) { g_team = on; }
 
 template <int KIND, class Rb>
 static int run(int n_clips, const dm_clip_t* clips, int n, const float* qpos, const float* qvel, const float* action,
@@ -52,7 +57,12 @@ static int run(int n_clips, const dm_clip_t* clips, int n, const float* qpos, co
                torque ? torque + (size_t)e * Rb::NU : nullptr};
     EnvState st{idx[e], ep_len[e], clip ? clip[e] : 0};
     StepOut so;
-    env_step<KIND, Rb, ArrayIO, true>(io, cs, cs.rows, st, contact ? contact[e] : 0u, so);
+    if (g_team) {
+      write_torque<Rb>(io);
+      team_step_serial<KIND, Rb, true>(io, io, cs, st, contact ? contact[e] : 0u, so);
+    } else {
+      env_step<KIND, Rb, ArrayIO, true>(io, cs, cs.rows, st, contact ? contact[e] : 0u, so);
+    }
     idx[e] = st.idx; ep_len[e] = st.ep_len;
     if (clip && KIND == KIND_COMBINED) clip[e] = st.clip;
     reward[e] = so.reward; done[e] = so.done; reason[e] = so.reason;

@@ -109,9 +109,10 @@ def oracle_clip_structs(robot, motions, combined=False):
 class HarnessBackend:
     """tests/host_harness: the kernel's per-env arithmetic compiled for the CPU (not the product)."""
 
-    def __init__(self, robot, kind, motions):
+    def __init__(self, robot, kind, motions, team=False):
         import ctypes as C
         import subprocess
+        self.team = bool(team)
         d = os.path.join(os.path.dirname(os.path.abspath(__file__)), "host_harness")
         so = os.path.join(d, "libhostharness.so")
         srcs = [os.path.join(d, "harness.cpp")]
@@ -140,6 +141,7 @@ class HarnessBackend:
         reason = np.zeros(n, np.uint8)
         torque = np.zeros((n, self.nu), np.float32)
         terms = np.zeros((n, 8), np.float32)
+        self.L.hh_set_team(1 if self.team else 0)
         rc = self.L.hh_step(self.robot_id, self.kind, len(self.clips), self.clips, n, np_ptr(qpos), np_ptr(qvel),
                             np_ptr(action), np_ptr(contact), np_ptr(idx), np_ptr(ep_len), np_ptr(clip), np_ptr(obs),
                             np_ptr(reward), np_ptr(done), np_ptr(reason), np_ptr(torque), np_ptr(terms))

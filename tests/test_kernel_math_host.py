@@ -13,22 +13,26 @@ CB = replay.load("combined_steps.npz")
 _backends = {}
 
 
-def backend(z, name):
+def backend(z, name, team=False):
     robot, kind, motions = replay.scenario_motions(z, name)
-    key = (robot, kind, tuple(motions))
+    key = (robot, kind, tuple(motions), team)
     if key not in _backends:
-        _backends[key] = replay.HarnessBackend(robot, kind, motions)
+        _backends[key] = replay.HarnessBackend(robot, kind, motions, team=team)
     return _backends[key]
 
 
+# team = False: the thread-per-environment step (dm_step.cuh + generated/robot_*.cuh: K1a, reset);
+# team = True: the team kernel's arithmetic (dm_team_core.cuh + generated/parts_*.cuh: K1c), its four parts run in turn
+@pytest.mark.parametrize("team", [False, True])
 @pytest.mark.parametrize("name", replay.scenarios(DP))
-def test_dpenv_kernel_math(name):
-    replay.assert_matches_golden(DP, name, replay.replay_batched(DP, name, backend(DP, name)))
+def test_dpenv_kernel_math(name, team):
+    replay.assert_matches_golden(DP, name, replay.replay_batched(DP, name, backend(DP, name, team)))
 
 
+@pytest.mark.parametrize("team", [False, True])
 @pytest.mark.parametrize("name", replay.scenarios(CB))
-def test_combined_kernel_math(name):
-    replay.assert_matches_golden(CB, name, replay.replay_batched(CB, name, backend(CB, name)))
+def test_combined_kernel_math(name, team):
+    replay.assert_matches_golden(CB, name, replay.replay_batched(CB, name, backend(CB, name, team)))
 
 
 def test_torque_matches_oracle():
