@@ -13,9 +13,6 @@
 #include "dm_fk_table.cuh"
 #include "generated/robot_humanoid3d.cuh"
 #include "generated/robot_unitree_g1.cuh"
-#include "dm_team_core.cuh"
-#include "generated/parts_humanoid3d.cuh"
-#include "generated/parts_unitree_g1.cuh"
 
 namespace dm {
 
@@ -92,10 +89,7 @@ __global__ void __launch_bounds__(128) step_strided_kernel(const __grid_constant
     st.clip = p.clip ? p.clip[env] : 0;
     const uint32_t contact = p.contact ? p.contact[env] : 0u;
     StepOut so;
-    // the team kernel's arithmetic, its four parts run in turn by this one thread: a batch's tail (and an SoA batch)
-    // gets bit for bit the rows the team kernel would have produced
-    write_torque<Rb>(io);
-    team_step_serial<KIND, Rb, TERMS>(io, io, p.cs, st, contact, so);
+    env_step<KIND, Rb, StridedIO, TERMS>(io, p.cs, p.cs.rows, st, contact, so);
     finish_env<KIND, Rb, TERMS>(p, env, st, so);
   }
 }

@@ -77,7 +77,7 @@ struct dm_handle {
   int copy_threads = -1;           // -1 = auto (3 helpers when the machine has the cores), DM_COPY_THREADS overrides
   // bookkeeping
   long long launches = 0;
-  int variant = -1;  // -1 auto (team kernel), 0 strided only, 1 tile kernel (K1b), 2 team kernel (K1c)
+  int variant = -1;  // -1 auto (= 1), 0 strided only (K1a), 1 tile kernel (K1b), 2 team kernel (K1c; opt-in)
   unsigned long long* d_team_trace = nullptr;  // DM_TEAM_TRACE: device buffer [32] of %globaltimer marks (printed at destroy)
   int team_maxt = 0, team_nin = 0, team_teams = 0, team_table = -1;  // tuning knobs of the team kernel (DM_TEAM_*; 0 / -1 = auto)
   int contact_mode = 0;  // DM_CONTACT_*
@@ -457,7 +457,7 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
                            reinterpret_cast<uintptr_t>(a->obs) | reinterpret_cast<uintptr_t>(a->action) |
                            reinterpret_cast<uintptr_t>(a->torque)) & 15u) == 0;
     int tiled = 0;
-    const bool team = h->variant < 0 || h->variant == 2;
+    const bool team = h->variant == 2;
     if (p.aos && team && aligned && a->n >= 32) {
       // K1c: tiles of 32 environments, one team of four warps per tile (dm_team_kernel.cuh)
       using MC = TeamCfg<KIND, Rb>;
@@ -497,7 +497,7 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
       cudaError_t e = launch_team<KIND, Rb>(tl, q, ex);
       CU(h, e);
       h->launches++;
-    } else if (p.aos && h->variant == 1 && aligned && a->n >= TC::TE) {
+    } else if (p.aos && !team && h->variant != 0 && aligned && a->n >= TC::TE) {
       tiled = a->n / TC::TE * TC::TE;
       timing_begin(h, s);
     } else {
@@ -1106,7 +1106,7 @@ extern "C" int dm_set_contact_mode(dm_handle* h, int mode) {
   return DM_OK;
 }
 extern "C" int dm_set_kernel_variant(dm_handle* h, int variant) {
-  if (!h || variant < -1 || variant > 1) return fail(h, DM_E_ARG, "dm_set_kernel_variant: variant must be -1, 0 or 1");
+  if (!h || variant < -1 || variant > 2) return fail(h, DM_E_ARG, "dm_set_kernel_variant: variant must be -1, 0, 1 or 2");
   h->variant = variant;
   return DM_OK;
 }

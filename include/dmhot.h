@@ -218,7 +218,9 @@ int dm_set_timing(dm_handle* h, int enabled);
  *                      caller's words are ignored.  Restated from MuJoCo 2.1 (parity unpinned: no MuJoCo here). */
 enum { DM_CONTACT_CALLER = 0, DM_CONTACT_FROM_FK = 1 };
 int dm_set_contact_mode(dm_handle* h, int mode);
-/* 0 = generic strided kernel, 1 = shared-memory tile kernel with TMA bulk copies (AoS only); default auto */
+/* 0 = generic strided kernel (K1a), 1 = shared-memory tile kernel with TMA bulk copies (K1b, AoS only), 2 = team kernel
+ * (K1c, AoS only: one environment split over four warps, rotation-matrix FK; results agree with 0 / 1 to fp32 round-off,
+ * not bit for bit); default -1 = auto = 1 */
 int dm_set_kernel_variant(dm_handle* h, int variant);
 
 /* ---- policy inference on the device -------------------------------------------------------------

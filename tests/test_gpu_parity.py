@@ -56,3 +56,35 @@ def test_product_loader_tables_match_oracle(robot, motion):
     np.testing.assert_allclose(np.asarray(m.data_vel), np.asarray(t.data_vel), rtol=0, atol=1e-9)
     np.testing.assert_allclose(np.asarray(m.data_body_xpos), np.asarray(t.data_body_xpos), rtol=0, atol=1e-12)
     np.testing.assert_allclose(np.asarray(m.data_geom_xpos), np.asarray(t.data_geom_xpos), rtol=0, atol=1e-12)
+
+
+class _Tiled:
+    """A golden file with every scenario's rows repeated up to a whole number of 32-environment tiles, so that the team
+    kernel (variant 2, tiles of 32) produces every row and none falls to the strided tail."""
+
+    def __init__(self, z, name, reps):
+        self.z, self.name, self.reps = z, name, reps
+
+    def __getitem__(self, key):
+        a = self.z[key]
+        if key.endswith("/meta"):
+            return a
+        return np.concatenate([a] * self.reps, 0)[:self.rows()]
+
+    def rows(self):
+        T = self.z[self.name + "/qpos"].shape[0]
+        return T * self.reps // 32 * 32
+
+
+@pytest.mark.parametrize("name", replay.scenarios(DP) + replay.scenarios(CB))
+def test_team_kernel_golden(name):
+    """K1c (dm_set_kernel_variant 2: one environment over four warps, rotation-matrix FK) against the same goldens."""
+    z = DP if name in replay.scenarios(DP) else CB
+    T = z[name + "/qpos"].shape[0]
+    tz = _Tiled(z, name, reps=max(2, -(-64 // T)))
+    assert tz.rows() >= 32 and tz.rows() % 32 == 0
+    be = backend(z, name, variant=2)
+    k0 = be.hp.launch_count()
+    got = replay.replay_batched(tz, name, be)
+    assert be.hp.launch_count() == k0 + 1  # one launch: the team kernel took every row
+    replay.assert_matches_golden(tz, name, got)
