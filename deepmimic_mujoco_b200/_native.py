@@ -72,7 +72,8 @@ SYMBOLS = ["dm_abi_version", "dm_create", "dm_destroy", "dm_last_error", "dm_get
            "dm_upload_clips", "dm_compile_clips", "dm_get_compiled_clip", "dm_get_packed_rows", "dm_step", "dm_reset", "dm_step_host", "dm_reset_host", "dm_host_buffers",
            "dm_stats_zero", "dm_stats_device_ptr", "dm_stats_read", "dm_launch_count", "dm_step_kernel_time",
            "dm_set_timing", "dm_set_kernel_variant", "dm_set_contact_mode", "dm_set_host_mode", "dm_policy_upload", "dm_policy_set_normalizer",
-           "dm_policy_normalizer_from_stats", "dm_policy_act", "dm_set_policy_variant"]
+           "dm_policy_normalizer_from_stats", "dm_policy_act", "dm_set_policy_variant", "dm_batch_stats_noalloc"]
+NOALLOC_MAX_OBS_DIM, NOALLOC_MAX_ENVS = 125, 1 << 22
 
 _lib = None
 
@@ -116,6 +117,7 @@ def lib():
     L.dm_policy_normalizer_from_stats.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_void_p]
     L.dm_policy_act.argtypes = [C.c_void_p, C.POINTER(PolicyArgs)]
     L.dm_set_policy_variant.argtypes = [C.c_void_p, C.c_int]
+    L.dm_batch_stats_noalloc.argtypes = [C.c_int, C.c_int32, C.c_int32] + [C.c_void_p] * 7
     _lib = L
     return L
 

@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -1269,5 +1270,113 @@ extern "C" int dm_policy_act(dm_handle* h, const dm_policy_args* a) {
   policy_mlp_kernel<<<grid, 256, kPolicySmemBytes, (cudaStream_t)a->stream>>>(p);
   h->launches++;
   CU(h, cudaGetLastError());
+  return DM_OK;
+}
+
+// ---- dm_batch_stats_noalloc: the statistics reduction (K4) without any allocation ----------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The existing route to these sums --
+// dm_step(accumulate_stats = 1) + dm_stats_read -- keeps its accumulators in memory cudaMalloc'd per handle; this variant
+// of stats_kernel keeps its scratch (per-block partial sums) in a file-scope device array instead and calls no cudaMalloc,
+// cudaFree or allocating library routine.
+//   * Size: kNoAllocBlocks x kNoAllocRow doubles = 256 KiB, held by every GPU that loads the library until exit.
+//   * Limits: obs_dim <= DM_NOALLOC_MAX_OBS_DIM (6 + 2 obs_dim <= kNoAllocRow), n <= DM_NOALLOC_MAX_ENVS.
+//   * Every call shares the array and it keeps the last call's contents.  Nothing in it has to start at zero: stage 1
+//     WRITES (never adds to) the rows of the blocks it launches, stage 2 reads exactly those rows, so stale rows of an
+//     earlier, larger call are never read.  Calls that overlap on the GPU (two streams, two host threads) RACE on the
+//     array: serialise them (one stream, or an event between them).
+//   * In host code `g_noalloc_scratch` is a host-side stand-in, not a device address; the address the kernels get comes
+//     from cudaGetSymbolAddress, once per device with that device current.
+constexpr int kNoAllocRow = 256;     // doubles per block: [6 scalars | sum obs[D] | sum obs^2[D]], D <= 125
+constexpr int kNoAllocBlocks = 128;  // stage-1 blocks at most
+static __device__ __align__(256) double g_noalloc_scratch[kNoAllocBlocks * kNoAllocRow];
+static double* g_noalloc_ptr[64] = {};  // per device: device address of g_noalloc_scratch
+static std::mutex g_noalloc_mutex;
+
+// stage 1: block b reduces its slab of environments into scratch row b (blockDim = (32, 8); fixed summation order)
+static __global__ void __launch_bounds__(256) stats_partial_kernel(int n, int D, const float* __restrict__ obs,
+                                                                   const float* __restrict__ reward, const uint8_t* __restrict__ done,
+                                                                   const float* __restrict__ ep_return, const int* __restrict__ ep_len,
+                                                                   double* __restrict__ scratch) {
+  __shared__ double sh[8][64];
+  const int lane = threadIdx.x, wy = threadIdx.y;
+  const int per_block = (n + gridDim.x - 1) / gridDim.x;
+  const int e0 = blockIdx.x * per_block, e1 = min(n, e0 + per_block);
+  double* row = scratch + (size_t)blockIdx.x * kNoAllocRow;
+  if (wy == 0) {  // the six scalars: lanes walk environments
+    double c = 0, sr = 0, srr = 0, nd = 0, ser = 0, sel = 0;
+    for (int e = e0 + lane; e < e1; e += 32) {
+      const double r = reward[e];
+      c += 1.0; sr += r; srr += r * r;
+      if (done[e]) {
+        nd += 1.0;
+        if (ep_return) ser += ep_return[e];
+        if (ep_len) sel += ep_len[e];
+      }
+    }
+    c = warp_sum(c); sr = warp_sum(sr); srr = warp_sum(srr); nd = warp_sum(nd); ser = warp_sum(ser); sel = warp_sum(sel);
+    if (lane == 0) { row[0] = c; row[1] = sr; row[2] = srr; row[3] = nd; row[4] = ser; row[5] = sel; }
+  }
+  for (int j0 = 0; j0 < D; j0 += 32) {  // observation columns: lanes walk columns of a row (coalesced), warps walk rows
+    const int j = j0 + lane;
+    double s = 0, ss = 0;
+    if (j < D)
+      for (int e = e0 + wy; e < e1; e += 8) {
+        const double v = obs[(long long)e * D + j];
+        s += v; ss += v * v;
+      }
+    sh[wy][lane] = s;
+    sh[wy][32 + lane] = ss;
+    __syncthreads();
+    if (wy == 0 && j < D) {
+      double a = 0, b = 0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) { a += sh[w][lane]; b += sh[w][32 + lane]; }
+      row[6 + j] = a;
+      row[6 + D + j] = b;
+    }
+    __syncthreads();
+  }
+}
+// stage 2: out[j] = sum over the blocks of stage 1, in block order
+static __global__ void __launch_bounds__(kNoAllocRow) stats_final_kernel(int blocks, int n_stats, const double* __restrict__ scratch,
+                                                                         double* __restrict__ out) {
+  const int j = threadIdx.x;
+  if (j >= n_stats) return;
+  double v = 0;
+  for (int b = 0; b < blocks; ++b) v += scratch[(size_t)b * kNoAllocRow + j];
+  out[j] = v;
+}
+
+extern "C" int dm_batch_stats_noalloc(int device, int32_t n, int32_t obs_dim, const float* obs, const float* reward,
+                                      const uint8_t* done, const float* ep_return, const int32_t* ep_len, double* out_stats,
+                                      void* stream) {
+  if (n < 0 || n > DM_NOALLOC_MAX_ENVS)
+    return fail(nullptr, DM_E_ARG, "dm_batch_stats_noalloc: n = %d is outside [0, %d] (DM_NOALLOC_MAX_ENVS)", n, DM_NOALLOC_MAX_ENVS);
+  if (obs_dim < 1 || obs_dim > DM_NOALLOC_MAX_OBS_DIM)
+    return fail(nullptr, DM_E_ARG, "dm_batch_stats_noalloc: obs_dim = %d is outside [1, %d] (DM_NOALLOC_MAX_OBS_DIM: the static scratch "
+                "holds %d doubles per block)", obs_dim, DM_NOALLOC_MAX_OBS_DIM, kNoAllocRow);
+  static_assert(6 + 2 * DM_NOALLOC_MAX_OBS_DIM <= kNoAllocRow, "scratch row too short");
+  if (!out_stats || (n > 0 && (!obs || !reward || !done)))
+    return fail(nullptr, DM_E_ARG, "dm_batch_stats_noalloc: a required buffer is NULL (obs reward done out_stats)");
+  if (device < 0 || device >= 64) return fail(nullptr, DM_E_ARG, "dm_batch_stats_noalloc: device %d out of range", device);
+  CU(nullptr, cudaSetDevice(device));
+  double* scratch;
+  {
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device]) {  // once per device, with that device current
+      void* p = nullptr;
+      CU(nullptr, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+      g_noalloc_ptr[device] = (double*)p;
+    }
+    scratch = g_noalloc_ptr[device];
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  int blocks = (n + 2047) / 2048;
+  blocks = blocks < 1 ? 1 : (blocks > kNoAllocBlocks ? kNoAllocBlocks : blocks);
+  stats_partial_kernel<<<blocks, dim3(32, 8), 0, s>>>(n, obs_dim, obs, reward, done, ep_return, ep_len, scratch);
+  CU(nullptr, cudaGetLastError());
+  stats_final_kernel<<<1, kNoAllocRow, 0, s>>>(blocks, 6 + 2 * obs_dim, scratch, out_stats);
+  CU(nullptr, cudaGetLastError());
   return DM_OK;
 }

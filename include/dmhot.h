@@ -204,6 +204,26 @@ int dm_stats_zero(dm_handle* h, void* stream);
 int dm_stats_device_ptr(dm_handle* h, double** dev_ptr, int32_t* n); /* for an in-place NCCL all-reduce */
 int dm_stats_read(dm_handle* h, double* host_out, void* stream);
 
+/* dm_batch_stats_noalloc -- NO COUNTERPART IN THE REFERENCE.
+ * The same statistics vector as above for ONE batch, computed without any allocation: no cudaMalloc, cudaFree or
+ * allocating library routine is called, so it can be used where those are forbidden (CUDA graph capture, tight serving
+ * loops).  Its scratch (per-block partial sums) is a file-scope static __device__ array of 256 KiB that every GPU which
+ * loads the library holds until exit.  No handle is needed.
+ *   device      CUDA device ordinal (made current)
+ *   n, obs_dim  environments in the batch, observation width; n <= DM_NOALLOC_MAX_ENVS, 1 <= obs_dim <=
+ *               DM_NOALLOC_MAX_OBS_DIM, anything beyond is rejected with DM_E_ARG and a message in dm_last_error(NULL)
+ *   obs [n, obs_dim] row-major, reward [n], done [n]    device pointers, required
+ *   ep_return [n], ep_len [n]                            device pointers or NULL (their sums are then 0)
+ *   out_stats   device double[6 + 2 obs_dim], fully overwritten:
+ *               [count, sum r, sum r^2, n_done, sum ep_return(done), sum ep_len(done), sum obs[D], sum obs^2[D]]
+ *   stream      cudaStream_t (NULL = default stream); asynchronous
+ * Every call shares the one scratch array: calls that overlap on the GPU (different streams or host threads without
+ * an ordering between them) race.  Results are deterministic (fixed summation order, no atomics). */
+#define DM_NOALLOC_MAX_OBS_DIM 125
+#define DM_NOALLOC_MAX_ENVS (1 << 22)
+int dm_batch_stats_noalloc(int device, int32_t n, int32_t obs_dim, const float* obs, const float* reward, const uint8_t* done,
+                           const float* ep_return, const int32_t* ep_len, double* out_stats, void* stream);
+
 /* launch bookkeeping for bench.py ("gpu_launches") */
 int dm_launch_count(const dm_handle* h, int64_t* kernels);
 /* name + average device time (CUDA events on the launch stream) of the step kernel since the last call
