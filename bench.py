@@ -26,6 +26,7 @@ sys.path.insert(0, REPO)
 
 BYTES_PER_ENV_STEP = {("humanoid3d", 0): 793, ("unitree_g1", 0): 953, ("unitree_g1", 1): 1021}
 L2_BYTES = 126e6
+STATE_SEED = 1234  # rank r's headline batches: synth_states(..., seed = STATE_SEED + r) on the CPU generator
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE step-kernel launch from `ncu --set full` captures of this very
 # command (profiles/r01_step_tile_s18_*_ncu_full_summary.txt), keyed by (robot, env kind, envs per GPU); at 4096 envs the
 # 1.7 MB of outputs are still dirty in L2 when the kernel ends, so only the reads reach DRAM inside the launch
@@ -47,7 +48,13 @@ def parse():
     ap.add_argument("--layout", default="aos", choices=["aos", "soa"])
     ap.add_argument("--variant", type=int, default=-1)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--allreduce-every", type=int, default=64)
+    ap.add_argument("--allreduce-every", type=int, default=1, help="steps between two statistics collectives (N > 1); BASELINE "
+                    "configs[2] asks for one EVERY step")
+    ap.add_argument("--collective", default="auto", choices=["auto", "reduce", "nccl", "off"],
+                    help="auto: dm_step issues the device-side exchange itself on a side stream (overlaps the next step); reduce: "
+                         "the same exchange launched explicitly between the steps; nccl: snapshot + ncclAllReduce + commit")
+    ap.add_argument("--collective-at-1", action="store_true", help="run the collective's local form at N = 1 too (cost probe)")
+    ap.add_argument("--no-configs", action="store_true", help="skip the BASELINE configs block (configs 3, 4, 5, 1 M row)")
     ap.add_argument("--no-stats", action="store_true")
     ap.add_argument("--no-sweep", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
@@ -190,6 +197,8 @@ class Workload:
         if args.states == "recorded":
             path = args.recording or os.path.join(REPO, "tests", "golden", "recorded_%s_%s.json" % (self.hp.robot, args.motion.split(",")[0]))
             s = recorded_states(self.hp, n_envs, self.B, path, device)
+        elif getattr(args, "host_seeded", False):  # the headline workload: the CPU arm draws the SAME numbers (cpu_states)
+            s = {k: v.to(device) for k, v in synth_states(self.hp, n_envs, self.B, seed, torch.device("cpu")).items()}
         else:
             s = synth_states(self.hp, n_envs, self.B, seed, device)
         self.soa = args.layout == "soa"
@@ -227,41 +236,61 @@ class Workload:
                      self.ep_return[b], soa_ld=(self.n if self.soa else 0), stats=self.stats)
 
 
-def timed_region(wl, steps, warmup, world, allreduce_every, stats_t):
-    """W untimed + exactly K timed steps, barrier + synchronize on both sides, CUDA events, max over ranks."""
+def timed_region(wl, steps, warmup, world, every, coll, mode):
+    """W untimed + exactly K timed steps, barrier + synchronize on both sides, CUDA events, max over ranks.
+    coll: the statistics collective (deepmimic_mujoco_b200.dist.StatsCollective) or None; with `mode` "auto" dm_step issues
+    the exchange itself behind every `every`-th step, otherwise it is launched here between the steps."""
     import torch
     import torch.distributed as dist
-    from deepmimic_mujoco_b200 import dist as dmdist
+    auto = coll is not None and mode == "auto" and coll.auto(every)
 
     def run(k):
         for i in range(k):
             wl.step()
-            if world > 1 and stats_t is not None and (i + 1) % allreduce_every == 0:
-                dmdist.allreduce_(stats_t)
+            if coll is not None and not auto and (i + 1) % every == 0:
+                coll.reduce()
 
-    run(warmup)
-    if world > 1 and stats_t is not None:  # the collective is part of the warm-up too (NCCL connects lazily on first use)
-        dmdist.allreduce_(stats_t)
+    run(warmup)  # the collective is part of the warm-up too (peer mappings and NCCL connect lazily on first use)
+    if coll is not None:
+        if auto:
+            coll.reduce()  # nothing of the warm-up may still be in flight when the statistics are zeroed
+        coll.join()
     wl.restore()
-    if stats_t is not None:
+    torch.cuda.synchronize()
+    if wl.stats:
         wl.hp.stats_zero(torch.cuda.current_stream().cuda_stream)
+        if auto:
+            coll.auto(every)  # restart the step counter of the auto mode
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
+    if coll is not None and world > 1 and not os.environ.get("DM_BENCH_NO_ALIGN"):
+        # the host barrier releases the ranks tens of microseconds apart -- a tenth of a 20-step region at 4096 environments.
+        # One exchange of (zeroed) statistics lines the GPUs up to within the NVLink round trip before the clock starts.
+        coll.reduce()
+        coll.join()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     l0 = wl.hp.launch_count()
     e0.record()
     run(steps)
-    if world > 1 and stats_t is not None:
-        dmdist.allreduce_(stats_t)
+    probe_no_final = bool(os.environ.get("DM_BENCH_NO_FINAL"))  # probe only: the flush after the clock stops
+    if coll is not None and not probe_no_final:
+        if auto or steps % every:
+            coll.reduce()  # auto: collect the exchange still in flight and exchange what the last step added; else the remainder
+        coll.join()        # the timed region ends when the last exchange has ended
     e1.record()
+    if coll is not None and probe_no_final:
+        coll.reduce()
+        coll.join()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
     launches = wl.hp.launch_count() - l0
+    if auto:
+        coll.auto(0)
     if world > 1:
         t = torch.tensor([ms], device=wl.device, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -382,15 +411,50 @@ def e2e_region(args, steps, warmup, seed, local_rank=0, world=1):
 
 
 # ------------------------------------------------------------------------------------------- CPU baseline
-def _cpu_worker(conn, robot, motion, combined, n_envs, seed):
-    """One SubprocVecEnv-style worker: owns n_envs oracle envs, one (recv, step, send) per env per step
-    (message pattern of reference src/profile_subproc_dpenv.py:10-25)."""
+class _OracleHandle:
+    """What synth_states needs of a HotPath, built from the oracle's tables: the CPU arm never touches libdmhot."""
+
+    def __init__(self, robot, motions, combined):
+        from types import SimpleNamespace
+        from oracle.assets import load_model
+        from oracle.envs import tables_for
+        self.combined = combined
+        self.robot = "unitree_g1" if combined else robot
+        m = load_model(self.robot)
+        names = ["walk", "run", "getup_facedown_towalk"] if combined else list(motions)
+        self.mocaps = [tables_for(self.robot, n) for n in names]
+        self.clip_lens = [t.get_length() for t in self.mocaps] + ([180] if combined else [])
+        n_hand = 14 if self.robot == "unitree_g1" else 0
+        self.dims = SimpleNamespace(nq=m.nq, nv=m.nv, na=m.nu - n_hand, nu=m.nu)
+        self._ctrl = m.actuator_ctrlrange
+
+    def model_constants(self):
+        return dict(ctrl_lo=self._ctrl[:, 0].astype(np.float32), ctrl_hi=self._ctrl[:, 1].astype(np.float32))
+
+
+def cpu_states(args, n_envs, n_batches, seed):
+    """The GPU arm's headline state batches (same generator, same seed, CPU device) as float64 numpy for the oracle."""
+    import torch
+    oh = _OracleHandle(args.robot, args.motion.split(","), args.combined)
+    s = synth_states(oh, n_envs, n_batches, seed, torch.device("cpu"))
+    return {k: v.numpy() for k, v in s.items()}
+
+
+def _cpu_worker(conn, robot, motions, combined, n_envs, first_env, st):
+    """One SubprocVecEnv-style worker: owns n_envs oracle envs, one (recv, step, send) per env per step (message pattern
+    of reference src/profile_subproc_dpenv.py:10-25).  Env i of this worker is global env first_env + i: it starts from the
+    counters of the seeded batch and is stepped with that env's states."""
     from oracle.envs import MultiClipEnv, SingleClipEnv
-    import random
-    random.seed(seed)
-    envs = [MultiClipEnv() if combined else SingleClipEnv(motion, robot) for _ in range(n_envs)]
-    for e in envs:
-        e.reset()
+    envs = []
+    for i in range(n_envs):
+        g = first_env + i
+        if combined:
+            e = MultiClipEnv()
+            e.reset()
+        else:
+            e = SingleClipEnv(motions[int(st["clip"][0, g])], robot)
+            e.reset(idx_init=int(st["idx"][0, g]))
+        envs.append(e)
     conn.send("ready")
     while True:
         msg = conn.recv()
@@ -404,52 +468,83 @@ def _cpu_worker(conn, robot, motion, combined, n_envs, seed):
         conn.send((obs, rew, done, info))
 
 
-def cpu_baseline(args, seconds, procs=None):
+def cpu_single_process(args, steps=10000, seconds=None):
+    """BASELINE configs[0]: the reference's own single-process loop (src/profile_dpenv.py:6-10: 10 000 random-action steps,
+    reset on done) on the oracle with DPEnv(motion, robot); states = force_state from the seeded generator."""
+    from oracle.envs import MultiClipEnv, SingleClipEnv
+    motions = args.motion.split(",")
+    B = 64
+    st = cpu_states(args, 1, B, STATE_SEED)
+    env = MultiClipEnv() if args.combined else SingleClipEnv(motions[0], "unitree_g1" if args.combined else args.robot)
+    env.reset()
+    done_steps, t0 = 0, time.perf_counter()
+    for i in range(steps):
+        b = i % B
+        obs, rew, done, info = env.step(st["action"][b, 0].astype(np.float64), (st["qpos"][b, 0].astype(np.float64), st["qvel"][b, 0].astype(np.float64)),
+                                        int(st["contact"][b, 0]))
+        if done:
+            env.reset()
+        done_steps += 1
+        if seconds and time.perf_counter() - t0 > seconds:
+            break
+    dt = time.perf_counter() - t0
+    return dict(value=done_steps / dt, unit="env-steps/s", cores=1, ms_per_step=1e3 * dt / done_steps, steps=done_steps,
+                loop="reference src/profile_dpenv.py:6-10 (one process, one env, reset on done), %d steps" % done_steps)
+
+
+def cpu_baseline(args, seconds, procs=None, per=None):
     """The oracle (float64 numpy restatement of the reference, one env at a time in Python) run as the reference runs:
-    P worker processes connected by pipes, one message round trip per env per step."""
+    P worker processes connected by pipes, one message round trip per env per step.  The N_cpu = P x per environments are
+    environments [0, N_cpu) of the GPU arm's headline batches (same seeded generator); the rate is what is reported, not
+    an extrapolated time."""
     import multiprocessing as mp
-    from oracle.envs import SingleClipEnv, MultiClipEnv, tables_for
+    from oracle.envs import MultiClipEnv, tables_for
     P = procs or os.cpu_count() or 1
-    per = 4
+    per = per or max(1, 64 // P) * (2 if P <= 16 else 1)
+    n_cpu = P * per
+    while n_cpu % 32:  # N_cpu = 32 k (BASELINE.md section 4)
+        per += 1
+        n_cpu = P * per
     ctx = mp.get_context("fork")
     robot = "unitree_g1" if args.combined else args.robot
-    motion = args.motion.split(",")[0]
+    motions = args.motion.split(",")
+    B = 16
+    st = cpu_states(args, n_cpu, B, STATE_SEED)
     if args.combined:
         MultiClipEnv()
     else:
-        tables_for(robot, motion)  # build tables once before forking
-    probe = MultiClipEnv() if args.combined else SingleClipEnv(motion, robot)
-    rng = np.random.default_rng(0)
-    nq, nv, na = probe.model.nq, probe.model.nv, probe.action_dim
-    base_q = np.asarray(probe.mocap.data_config[0] if not args.combined else probe.walk_mocap.data_config[0])
-    base_v = np.asarray(probe.mocap.data_vel[0] if not args.combined else probe.walk_mocap.data_vel[0])
+        for m in motions:
+            tables_for(robot, m)  # build tables once before forking
+    f64 = {k: st[k].astype(np.float64) for k in ("qpos", "qvel", "action")}
     pipes, ps = [], []
     for p in range(P):
         a, b = ctx.Pipe()
-        pr = ctx.Process(target=_cpu_worker, args=(b, robot, motion, args.combined, per, p), daemon=True)
+        pr = ctx.Process(target=_cpu_worker, args=(b, robot, motions, args.combined, per, p * per, st), daemon=True)
         pr.start()
         pipes.append(a)
         ps.append(pr)
     for a in pipes:
         a.recv()
-    steps_done, t0 = 0, time.perf_counter()
+    steps_done, vec_steps, t0 = 0, 0, time.perf_counter()
     while time.perf_counter() - t0 < seconds:
+        b = vec_steps % B
         for i in range(per):  # vec step: send to every worker, then gather (step_async / step_wait)
-            for a in pipes:
-                q = base_q + np.concatenate([rng.normal(0, 0.02, 7), rng.normal(0, 0.05, nq - 7)])
-                v = base_v + rng.normal(0, 0.5, nv)
-                a.send((i, rng.uniform(-1, 1, na), q, v, int(rng.integers(0, 4))))
+            for p, a in enumerate(pipes):
+                g = p * per + i
+                a.send((i, f64["action"][b, g], f64["qpos"][b, g], f64["qvel"][b, g], int(st["contact"][b, g])))
             for a in pipes:
                 a.recv()
-        steps_done += per * P
+        steps_done += n_cpu
+        vec_steps += 1
     dt = time.perf_counter() - t0
     for a in pipes:
         a.send(None)
     for pr in ps:
         pr.join(timeout=2)
-    return dict(value=steps_done / dt, unit="env-steps/s", cores=P, kind="port",
-                sample="%d env-steps of the same workload (%s %s, %d envs in %d worker processes over pipes, %.1f s)" %
-                       (steps_done, robot, "combined" if args.combined else motion, per * P, P, dt))
+    return dict(value=steps_done / dt, unit="env-steps/s", cores=P, kind="port", n_cpu_envs=n_cpu, vec_steps=vec_steps,
+                sample="%d vec steps of environments [0, %d) of the GPU arm's seeded batches (%s %s; %d worker processes x %d envs "
+                       "over pipes, %.1f s); a RATE measured on that sample, not extrapolated from a time" %
+                       (vec_steps, n_cpu, robot, "combined" if args.combined else args.motion, P, per, dt))
 
 
 def reference_arm(args, rank):
@@ -460,12 +555,14 @@ def reference_arm(args, rank):
     P = os.cpu_count() or 1
     budget = min(90.0, max(6.0, 0.15 * (args.steps + args.warmup)))
     cb = cpu_baseline(args, budget, P)
+    cb["single_process"] = cpu_single_process(args, 10000, seconds=min(60.0, budget))
     line = {"impl": "reference", "metric": "env-steps/s (ref-lookup+FK+reward+obs+PD)", "value": cb["value"], "unit": "env-steps/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * args.envs / cb["value"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(args), "envs_per_gpu": args.envs,
-                       "note": "ms_per_step = time the CPU arm needs for one control step of all envs_per_gpu environments"},
+                       "note": "value = measured rate on the N_cpu-environment sample (cpu_baseline.sample); ms_per_step = what one "
+                               "control step of all envs_per_gpu environments would take at that rate"},
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -497,6 +594,68 @@ def emit(line):
     print(json.dumps(line), flush=True)
 
 
+def _variant_args(args, **kw):
+    d = dict(vars(args))
+    d.update(kw)
+    return argparse.Namespace(**d)
+
+
+def run_config(args, device, rank, world, envs_per_rank, steps, warmup, seed, with_coll, peak):
+    """One workload on every rank at once (weak or sharded: the caller picks envs_per_rank): device-timed steps with the
+    statistics collective every step when N > 1, plus the step kernel's own time and roofline fraction."""
+    import torch
+    from deepmimic_mujoco_b200 import dist as dmdist
+    wl = Workload(args, device, envs_per_rank, seed + rank, steps)
+    coll = None
+    if wl.stats and with_coll and (world > 1 or args.collective_at_1) and args.collective != "off":
+        coll = dmdist.StatsCollective(wl.hp, force_nccl=(args.collective == "nccl"))
+    ms, launches = timed_region(wl, steps, warmup, world, 1, coll, args.collective)
+    out = {"envs_total": envs_per_rank * world, "envs_per_gpu": envs_per_rank, "ms_per_step": ms / steps,
+           "env_steps_per_s": world * envs_per_rank * steps / (ms * 1e-3), "gpu_launches": int(launches)}
+    if coll is not None:
+        tot = coll.totals()
+        out["collective"] = {"mode": coll.mode, "issue": args.collective, "every": 1, "count": tot[0],
+                             "count_expected": float(world * envs_per_rank * steps)}
+        assert tot[0] == world * envs_per_rank * steps, "statistics count %r != N * E * steps = %r" % (tot[0], world * envs_per_rank * steps)
+    k_ms, _ = kernel_time(wl, min(steps, 50))
+    gbs = wl.bpe * envs_per_rank / (k_ms * 1e-3) / 1e9
+    out.update(kernel_ms=k_ms, GBps=gbs, frac=gbs / peak, bytes_per_env_step=wl.bpe)
+    tr = NCU_TRAFFIC.get((wl.hp.robot, wl.kind, envs_per_rank))
+    if tr:
+        out["traffic"], out["traffic_source"] = tr
+    wl.hp.close()
+    del wl
+    torch.cuda.empty_cache()
+    return out
+
+
+def configs_block(args, device, rank, world, peak):
+    """BASELINE.json configs 3, 4, 5 and the 1 M-env row of the north-star target, measured in this very run."""
+    steps, warmup = 20, 5
+    blk = {}
+    c3 = _variant_args(args, robot="humanoid3d", motion="spinkick,dance_b", combined=False, layout="aos", states="synthetic")
+    blk["config3_spinkick_dance_b_65536_sharded"] = run_config(c3, device, rank, world, 65536 // world, steps, warmup, 300, True, peak)
+    c4 = _variant_args(args, robot="unitree_g1", combined=True, layout="aos", states="synthetic")
+    blk["config4_g1_combined_262144_sharded"] = run_config(c4, device, rank, world, 262144 // world, steps, warmup, 400, True, peak)
+    if world > 1:
+        blk["config4_g1_combined_262144_per_gpu"] = run_config(c4, device, rank, world, 262144, steps, warmup, 410, True, peak)
+    h1 = _variant_args(args, robot="humanoid3d", motion="walk", combined=False, layout="aos", states="synthetic")
+    blk["target_humanoid3d_walk_1M_per_gpu"] = run_config(h1, device, rank, world, 1 << 20, steps, warmup, 500, True, peak)
+    blk["target_g1_combined_1M_per_gpu"] = run_config(c4, device, rank, world, 1 << 20, steps, warmup, 510, True, peak)
+    sweep = []
+    for e in range(10, 23):  # config 5: 2^10 .. 2^22 environments per GPU, both robots, every rank at once
+        row = {"envs_per_gpu": 1 << e}
+        for name, a in (("humanoid3d_walk", h1), ("g1_combined", c4)):
+            r = run_config(a, device, rank, world, 1 << e, 10, 3, 600 + e, False, peak)
+            row[name] = {k: r[k] for k in ("ms_per_step", "env_steps_per_s", "kernel_ms", "GBps", "frac")}
+        sweep.append(row)
+    blk["config5_sweep"] = sweep
+    if args.layout == "aos":  # the SoA layout at 1 M environments next to the row-major one
+        so = _variant_args(h1, layout="soa")
+        blk["layout_soa_humanoid3d_walk_1M"] = run_config(so, device, rank, world, 1 << 20, 10, 3, 700, False, peak)
+    return blk
+
+
 def main():
     args = parse()
     from deepmimic_mujoco_b200 import dist as dmdist
@@ -511,15 +670,21 @@ def main():
     device = torch.device("cuda", local_rank)
     peak, peak_src = peaks()
 
-    wl = Workload(args, device, args.envs, 1234 + rank, args.steps)
-    stats_t = dmdist.stats_tensor(wl.hp) if wl.stats else None
+    wl = Workload(_variant_args(args, host_seeded=args.envs <= 65536), device, args.envs, STATE_SEED + rank, args.steps)
+    coll = None
+    if wl.stats and (world > 1 or args.collective_at_1) and args.collective != "off":
+        coll = dmdist.StatsCollective(wl.hp, force_nccl=(args.collective == "nccl"))
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
         sampler.start()
-    ms, launches = timed_region(wl, args.steps, max(args.warmup, 3), world, args.allreduce_every, stats_t)
+    ms, launches = timed_region(wl, args.steps, max(args.warmup, 3), world, args.allreduce_every, coll, args.collective)
     clocks = sampler.stop() if sampler else None
     value = world * args.envs * args.steps / (ms * 1e-3)
-    stats_host = wl.hp.stats_read() if wl.stats else None
+    stats_host = None
+    if wl.stats:
+        stats_host = coll.totals() if coll is not None else wl.hp.stats_read()
+        want = (world if coll is not None else 1) * args.envs * args.steps
+        assert stats_host[0] == want, "statistics count %r != %r" % (stats_host[0], want)
 
     # roofline of the dominant kernel at this workload
     k_ms, k_n = kernel_time(wl, min(args.steps, 200))
@@ -537,37 +702,42 @@ def main():
             "config": {"workload": workload_name(args), "layout": args.layout, "state_batches": wl.B,
                        "l2_policy": "inputs larger than L2: %d distinct resident batches (%.0f MB) cycled" %
                                     (wl.B, wl.B * bytes_per_launch / 1e6),
-                       "stats": wl.stats, "allreduce_every": args.allreduce_every if world > 1 else None},
+                       "stats": wl.stats,
+                       "collective": None if coll is None else {"mode": coll.mode, "issue": args.collective, "every": args.allreduce_every,
+                                                                "why_not_peer": coll.why_not_peer}},
             "roofline": roof, "gpu_launches": int(launches), "clocks": clocks}
     if stats_host is not None:
         m = dmdist.moments(stats_host, wl.hp.obs_dim)
-        line["stats"] = {"count": m["count"], "reward_mean": m["reward_mean"], "done_rate": m["done_rate"]}
-
+        line["stats"] = {"count": m["count"], "count_expected": float((world if coll is not None else 1) * args.envs * args.steps),
+                         "scope": "all ranks" if coll is not None else "this rank", "reward_mean": m["reward_mean"], "done_rate": m["done_rate"]}
     if rank == 0 and not args.no_sweep:
-        sweep = []
-        for n in [int(x) for x in args.sweep_envs.split(",") if x]:
-            w2 = Workload(args, device, n, 99, 20)
-            for _ in range(5):
-                w2.step()
-            km, kn = kernel_time(w2, 20)
-            a = w2.bpe * n / (km * 1e-3) / 1e9
-            sweep.append({"envs": n, "kernel_ms": km, "env_steps_per_s": n / (km * 1e-3), "GBps": a, "frac": a / peak})
-            del w2
-            torch.cuda.empty_cache()
-        line["sweep"] = sweep
         line["policy"] = policy_time(wl.hp, device, 1048576)
+    wl.hp.close()
+    del wl
+    torch.cuda.empty_cache()
+    if not args.no_configs and not args.no_sweep:  # every rank takes part (sharded workloads, the collective)
+        blk = configs_block(args, device, rank, world, peak)
+        if rank == 0:
+            line["configs"] = blk
+            # kept for readers of earlier rounds' lines: the two sizes the round-1 `sweep` key held
+            line["sweep"] = [dict(envs=r["envs_per_gpu"], **r["humanoid3d_walk"]) for r in blk["config5_sweep"]
+                             if r["envs_per_gpu"] in (65536, 1048576)]
     if world > 1:
         import torch.distributed as dist
         dist.barrier()
     if not args.no_e2e:  # every rank steps its own environments through the host API at the same time
-        del wl
-        torch.cuda.empty_cache()
         e2e = e2e_region(args, min(args.steps, 200), 20, 7, local_rank, world)
         if rank == 0:
             line["e2e"] = e2e
+        if rank == 0 and world == 1 and "configs" in line:  # BASELINE configs[3] through the same host API
+            c4 = _variant_args(args, robot="unitree_g1", combined=True, envs=262144)
+            r = e2e_region(c4, 8, 3, 9, local_rank, world)
+            line["configs"]["config4_g1_combined_262144_sharded"]["e2e"] = {k: r[k] for k in ("value", "unit", "ms_per_step", "h2d_bytes_per_step", "d2h_bytes_per_step")}
+            line["configs"]["config4_g1_combined_262144_sharded"]["e2e"]["pinned"] = r["pinned"]
     if rank == 0:
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline(args, args.cpu_seconds)
+            line["cpu_baseline"]["single_process"] = cpu_single_process(args, 10000, seconds=args.cpu_seconds)
         RESULT.append(line)
     if world > 1:
         import torch.distributed as dist

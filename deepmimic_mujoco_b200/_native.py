@@ -72,7 +72,10 @@ SYMBOLS = ["dm_abi_version", "dm_create", "dm_destroy", "dm_last_error", "dm_get
            "dm_upload_clips", "dm_compile_clips", "dm_get_compiled_clip", "dm_get_packed_rows", "dm_step", "dm_reset", "dm_step_host", "dm_reset_host", "dm_host_buffers",
            "dm_stats_zero", "dm_stats_device_ptr", "dm_stats_read", "dm_launch_count", "dm_step_kernel_time",
            "dm_set_timing", "dm_set_kernel_variant", "dm_set_contact_mode", "dm_set_host_mode", "dm_policy_upload", "dm_policy_set_normalizer",
-           "dm_policy_normalizer_from_stats", "dm_policy_act", "dm_set_policy_variant", "dm_batch_stats_noalloc"]
+           "dm_policy_normalizer_from_stats", "dm_policy_act", "dm_set_policy_variant", "dm_batch_stats_noalloc",
+           "dm_stats_peer_export", "dm_stats_peer_import", "dm_stats_allreduce", "dm_stats_snapshot", "dm_stats_commit", "dm_stats_read_total",
+           "dm_stats_set_auto", "dm_stats_join"]
+IPC_HANDLE_BYTES = 64
 NOALLOC_MAX_OBS_DIM, NOALLOC_MAX_ENVS = 125, 1 << 22
 
 _lib = None
@@ -117,6 +120,14 @@ def lib():
     L.dm_policy_normalizer_from_stats.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_void_p]
     L.dm_policy_act.argtypes = [C.c_void_p, C.POINTER(PolicyArgs)]
     L.dm_set_policy_variant.argtypes = [C.c_void_p, C.c_int]
+    L.dm_stats_peer_export.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
+    L.dm_stats_peer_import.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]
+    L.dm_stats_allreduce.argtypes = [C.c_void_p, C.c_void_p]
+    L.dm_stats_snapshot.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.c_void_p]
+    L.dm_stats_commit.argtypes = [C.c_void_p, C.c_void_p]
+    L.dm_stats_read_total.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.dm_stats_set_auto.argtypes = [C.c_void_p, C.c_int32]
+    L.dm_stats_join.argtypes = [C.c_void_p, C.c_void_p]
     L.dm_batch_stats_noalloc.argtypes = [C.c_int, C.c_int32, C.c_int32] + [C.c_void_p] * 7
     _lib = L
     return L

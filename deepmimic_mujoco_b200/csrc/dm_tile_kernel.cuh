@@ -32,6 +32,7 @@
 // Batches that are not a multiple of 128 environments hand the remainder to the strided kernel (K1a).
 #pragma once
 #include "dm_kernels.cuh"
+#include "dm_peer.cuh"
 
 namespace dm {
 
@@ -159,6 +160,7 @@ struct TileExtra {
   int table_floats;  // packed clip table size (floats); staged in shared memory when TABLE_SMEM
   int nbuf;          // ring slots (>= groups per CTA); nbuf - groups tiles are always loading ahead of the groups
   int skip_compute;  // experiment: memory skeleton only (no env_step)
+  PeerParams peer;   // peer.enable: the launch has one CTA more than tiles need, the statistics exchange CTA (dm_peer.cuh)
 };
 
 __device__ __forceinline__ void group_sync(int group) {  // named barrier 1 + group, one group of threads
@@ -193,12 +195,13 @@ __global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_co
   float* s_row = reinterpret_cast<float*>(reinterpret_cast<char*>(s_ring + (size_t)nbuf * TC::BUF_FLOATS) +
                                           (STATS ? (size_t)n_groups * TC::ACC_BYTES : 0)) + (size_t)group * TE * RL::STRIDE;
   uint64_t* rbar = bars + TC::MAXBUF + 1 + (group < 3 ? group : 2);
-  // this CTA's tiles are blockIdx.x + j * gridDim.x, j = 0 .. nt-1; tile j sits in ring slot j % nbuf and is
+  // this CTA's tiles are blockIdx.x + j * ncta, j = 0 .. nt-1; tile j sits in ring slot j % nbuf and is
   // processed by group j % n_groups
-  const int nt = (int)blockIdx.x < x.n_tiles ? (x.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  const int ncta = (int)gridDim.x - (STATS && x.peer.enable ? 1 : 0);  // CTAs that walk tiles
+  const int nt = (int)blockIdx.x < x.n_tiles ? (x.n_tiles - 1 - (int)blockIdx.x) / ncta + 1 : 0;
   auto issue_load = [&](int j) {  // one thread
     const int slot = j % nbuf;
-    const long long f0 = ((long long)blockIdx.x + (long long)j * gridDim.x) * TE;
+    const long long f0 = ((long long)blockIdx.x + (long long)j * ncta) * TE;
     float* dst = s_ring + (size_t)slot * TC::BUF_FLOATS;
     const bool act = TC::ACT_FLOATS != 0 && p.torque != nullptr;
     mbar_expect_tx(bars + slot, sizeof(float) * (TE * (Rb::NQ + Rb::NV) + (act ? TC::ACT_FLOATS : 0)));
@@ -217,6 +220,16 @@ __global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_co
     if (gt < 4) g_done[gt] = 0.0;
   }
   __syncthreads();
+  if (STATS && x.peer.enable && (int)blockIdx.x == ncta) {
+    // The statistics exchange CTA (auto mode of the collective): once the previous step is complete it collects the
+    // exchange posted a step ago and posts the sums accumulated since, beside the tile CTAs' work on this step.
+    if (x.peer.enable == 2) return;  // debug (DM_PEER_DEBUG): an idle extra CTA
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (x.peer.enable == 3) return;  // debug: ... that only waits for the previous kernel
+    peer_fused_cta(x.peer);
+    return;
+  }
   // Everything up to here, the clip table and the motor constants touch nothing an earlier launch writes.  Under
   // programmatic dependent launch this prologue (and the launch latency in front of it) overlaps the tail of the
   // previous kernel in the stream; griddepcontrol.wait then blocks until that kernel has completed and its writes
@@ -335,7 +348,7 @@ __global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_co
     if (gt == 0) mbar_expect_tx(rbar, sizeof(float) * TE * RL::STRIDE);
     tma_load_1d(s_row + gt * RL::STRIDE, p.cs.rows + (size_t)row_i * RL::STRIDE, sizeof(float) * RL::STRIDE, rbar);
   };
-  auto tile_of = [&](int j) { return (int)blockIdx.x + j * (int)gridDim.x; };
+  auto tile_of = [&](int j) { return (int)blockIdx.x + j * ncta; };
   if (group < nt) {
     load_ahead(tile_of(group));
     if (ROW_STAGE) issue_rows();

@@ -46,6 +46,17 @@ struct dm_handle {
   ClipSet cs{};
   // statistics
   double* d_stats = nullptr;
+  // ... their collective (dm_peer.cuh): snapshot, global totals, sequence number, error word, peer-mapped buffers
+  double* d_snap = nullptr;
+  double* d_total = nullptr;
+  PeerState* d_peer_state = nullptr;
+  PeerComm* peer_comm[kPeerMaxWorld] = {};  // [peer_rank] = own cudaMalloc'd buffer, the others cudaIpc mappings
+  int peer_rank = 0, peer_world = 1;        // world 1 until dm_stats_peer_import has connected the ranks
+  int auto_every = 0;                       // dm_stats_set_auto: an exchange with every auto_every-th dm_step with statistics
+  long long auto_count = 0;
+  bool fuse_now = false, fused_done = false;  // this dm_step is due an exchange / the tile kernel carried it (exchange CTA)
+  cudaStream_t coll_stream = nullptr;       // side stream of the auto mode
+  cudaEvent_t coll_event = nullptr;
   // policy (K6)
   float* d_pol_packed = nullptr;  // weight chunks in consumption order
   uint8_t* d_pol_packed16 = nullptr;  // the same stream as fp16 hi / lo pairs for the tensor-core kernel
@@ -197,6 +208,15 @@ extern "C" int dm_destroy(dm_handle* h) {
   cudaFree(h->d_rows);
   cudaFree(h->d_state_rows);
   cudaFree(h->d_stats);
+  for (int r = 0; r < kPeerMaxWorld; ++r)
+    if (h->peer_comm[r]) {
+      if (r == h->peer_rank) cudaFree(h->peer_comm[r]); else cudaIpcCloseMemHandle(h->peer_comm[r]);
+    }
+  if (h->coll_stream) { cudaStreamSynchronize(h->coll_stream); cudaStreamDestroy(h->coll_stream); }
+  if (h->coll_event) cudaEventDestroy(h->coll_event);
+  cudaFree(h->d_snap);
+  cudaFree(h->d_total);
+  cudaFree(h->d_peer_state);
   cudaFree(h->d_pol_packed);
   cudaFree(h->d_pol_packed16);
   cudaFree(h->d_pol_bias);
@@ -436,6 +456,8 @@ static void timing_end(dm_handle* h, cudaStream_t s) {
 template <class T>
 static T* off(T* p, long long n) { return p ? p + n : p; }
 
+static PeerParams peer_params(const dm_handle* h, int enable);
+
 static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
   if (a->n == 0) return DM_OK;
   return dispatch(h, [&](auto rb, auto kind) -> int {
@@ -556,12 +578,18 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
                              smem + row_stage_bytes <= TC::SMEM_BUDGET;
       if (row_stage) smem += row_stage_bytes;
       TileExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float)), nbuf, h->skip_compute};
+      const bool fused = h->fuse_now && a->accumulate_stats;  // one more CTA: the statistics exchange (dm_peer.cuh)
+      if (fused) {
+        static const int dbg = getenv("DM_PEER_DEBUG") ? atoi(getenv("DM_PEER_DEBUG")) : 1;
+        ex.peer = peer_params(h, dbg);
+      }
       // the kernels themselves live in dm_tile_{h,g,c}.cu, one translation unit per (kind, robot)
-      TileLaunch tl{grid, G, smem, s, h->pdl != 0, a->terms != nullptr, a->accumulate_stats != 0,
+      TileLaunch tl{grid + (fused ? 1 : 0), G, smem, s, h->pdl != 0, a->terms != nullptr, a->accumulate_stats != 0,
                     row_stage ? 2 : (table_smem ? 1 : 0), wide ? 1 : (mid ? 2 : 0)};
       cudaError_t e = launch_tile<KIND, Rb>(tl, q, ex);
       CU(h, e);
       h->launches++;
+      if (fused) h->fused_done = true;
     }
     const int rest = a->n - tiled;
     if (rest) {
@@ -594,11 +622,25 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
   });
 }
 
+static int issue_exchange(dm_handle* h, cudaStream_t s);
+
 extern "C" int dm_step(dm_handle* h, const dm_step_args* a) {
   int rc = check_step_args(h, a, "dm_step");
   if (rc) return rc;
   CU(h, cudaSetDevice(h->device));
-  return launch_step(h, a, (cudaStream_t)a->stream);
+  // auto mode of the collective: every auto_every-th step with statistics carries an exchange -- as one extra CTA of the
+  // tile kernel where that kernel runs (the normal case), else as its own kernel on the side stream behind the step
+  const bool due = h->auto_every > 0 && a->accumulate_stats && a->n > 0 && (h->auto_count + 1) % h->auto_every == 0;
+  h->fuse_now = due;
+  h->fused_done = false;
+  rc = launch_step(h, a, (cudaStream_t)a->stream);
+  h->fuse_now = false;
+  if (rc) return rc;
+  if (h->auto_every > 0 && a->accumulate_stats && a->n > 0) ++h->auto_count;
+  if (!due || h->fused_done) return DM_OK;
+  CU(h, cudaEventRecord(h->coll_event, (cudaStream_t)a->stream));
+  CU(h, cudaStreamWaitEvent(h->coll_stream, h->coll_event, 0));
+  return issue_exchange(h, h->coll_stream);
 }
 
 static int launch_reset(dm_handle* h, const dm_reset_args* a, cudaStream_t s) {
@@ -1060,6 +1102,11 @@ extern "C" int dm_stats_zero(dm_handle* h, void* stream) {
   if (!h) return fail(nullptr, DM_E_ARG, "dm_stats_zero: NULL handle");
   CU(h, cudaSetDevice(h->device));
   CU(h, cudaMemsetAsync(h->d_stats, 0, sizeof(double) * h->dims.n_stats, (cudaStream_t)stream));
+  if (h->coll_stream) CU(h, cudaStreamSynchronize(h->coll_stream));
+  if (h->d_total) {  // the collective's snapshot and global totals restart with the accumulators (not its sequence number)
+    CU(h, cudaMemsetAsync(h->d_snap, 0, sizeof(double) * kPeerStride, (cudaStream_t)stream));
+    CU(h, cudaMemsetAsync(h->d_total, 0, sizeof(double) * kPeerStride, (cudaStream_t)stream));
+  }
   return DM_OK;
 }
 extern "C" int dm_stats_device_ptr(dm_handle* h, double** dev_ptr, int32_t* n) {
@@ -1212,7 +1259,7 @@ extern "C" int dm_policy_normalizer_from_stats(dm_handle* h, float eps, float cl
   if (!h->d_pol_norm) return fail(h, DM_E_STATE, "dm_policy_normalizer_from_stats: no policy uploaded (call dm_policy_upload first)");
   if (h->dims.obs_dim > PMAX_IN) return fail(h, DM_E_ARG, "dm_policy_normalizer_from_stats: obs_dim %d > %d", h->dims.obs_dim, PMAX_IN);
   CU(h, cudaSetDevice(h->device));
-  policy_norm_from_stats_kernel<<<1, PMAX_IN, 0, (cudaStream_t)stream>>>(h->d_stats, h->dims.obs_dim, eps, h->d_pol_norm,
+  policy_norm_from_stats_kernel<<<1, PMAX_IN, 0, (cudaStream_t)stream>>>(h->d_total ? h->d_total : h->d_stats, h->dims.obs_dim, eps, h->d_pol_norm,
                                                                         h->d_pol_norm + 2 * PMAX_IN);
   h->launches++;
   CU(h, cudaGetLastError());
@@ -1378,5 +1425,155 @@ extern "C" int dm_batch_stats_noalloc(int device, int32_t n, int32_t obs_dim, co
   CU(nullptr, cudaGetLastError());
   stats_final_kernel<<<1, kNoAllocRow, 0, s>>>(blocks, 6 + 2 * obs_dim, scratch, out_stats);
   CU(nullptr, cudaGetLastError());
+  return DM_OK;
+}
+
+// ---- the statistics collective (K7, dm_peer.cuh) ------------------------------------------------------------------------
+static int peer_ensure(dm_handle* h) {  // device buffers of the collective, allocated on first use
+  if (h->d_total) return DM_OK;
+  CU(h, cudaSetDevice(h->device));
+  CU(h, cudaMalloc(&h->d_snap, sizeof(double) * kPeerStride));
+  CU(h, cudaMalloc(&h->d_total, sizeof(double) * kPeerStride));
+  CU(h, cudaMalloc(&h->d_peer_state, sizeof(PeerState)));
+  CU(h, cudaMemset(h->d_snap, 0, sizeof(double) * kPeerStride));
+  CU(h, cudaMemset(h->d_total, 0, sizeof(double) * kPeerStride));
+  CU(h, cudaMemset(h->d_peer_state, 0, sizeof(PeerState)));
+  return DM_OK;
+}
+
+extern "C" int dm_stats_peer_export(dm_handle* h, int32_t rank, int32_t world, void* handle_out) {
+  if (!h || !handle_out) return fail(h, DM_E_ARG, "dm_stats_peer_export: NULL argument");
+  if (world < 1 || world > kPeerMaxWorld || rank < 0 || rank >= world)
+    return fail(h, DM_E_ARG, "dm_stats_peer_export: rank %d / world %d (at most %d ranks: the GPUs of one box)", rank, world, kPeerMaxWorld);
+  if (h->dims.n_stats > kPeerStride) return fail(h, DM_E_STATE, "dm_stats_peer_export: %d statistics exceed the slot size", h->dims.n_stats);
+  if (h->peer_world > 1 || h->peer_comm[h->peer_rank]) return fail(h, DM_E_STATE, "dm_stats_peer_export: this handle is already part of a group");
+  int rc = peer_ensure(h);
+  if (rc) return rc;
+  static_assert(sizeof(cudaIpcMemHandle_t) == DM_IPC_HANDLE_BYTES, "cudaIpcMemHandle_t size");
+  PeerComm* c = nullptr;
+  CU(h, cudaMalloc(&c, sizeof(PeerComm)));
+  CU(h, cudaMemset(c, 0, sizeof(PeerComm)));
+  CU(h, cudaDeviceSynchronize());
+  cudaIpcMemHandle_t ih;
+  cudaError_t e = cudaIpcGetMemHandle(&ih, c);
+  if (e != cudaSuccess) {
+    cudaFree(c);
+    return fail(h, DM_E_CUDA, "dm_stats_peer_export: cudaIpcGetMemHandle: %s", cudaGetErrorString(e));
+  }
+  h->peer_rank = rank;
+  h->peer_comm[rank] = c;
+  memcpy(handle_out, &ih, sizeof ih);
+  return DM_OK;
+}
+
+extern "C" int dm_stats_peer_import(dm_handle* h, int32_t world, const void* handles) {
+  if (!h || !handles) return fail(h, DM_E_ARG, "dm_stats_peer_import: NULL argument");
+  if (!h->peer_comm[h->peer_rank]) return fail(h, DM_E_STATE, "dm_stats_peer_import: call dm_stats_peer_export first");
+  if (world < 1 || world > kPeerMaxWorld || h->peer_rank >= world) return fail(h, DM_E_ARG, "dm_stats_peer_import: world %d", world);
+  CU(h, cudaSetDevice(h->device));
+  for (int r = 0; r < world; ++r) {
+    if (r == h->peer_rank) continue;
+    cudaIpcMemHandle_t ih;
+    memcpy(&ih, (const char*)handles + (size_t)r * DM_IPC_HANDLE_BYTES, sizeof ih);
+    void* p = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&p, ih, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      for (int q = 0; q < r; ++q)
+        if (q != h->peer_rank && h->peer_comm[q]) { cudaIpcCloseMemHandle(h->peer_comm[q]); h->peer_comm[q] = nullptr; }
+      return fail(h, DM_E_CUDA, "dm_stats_peer_import: cudaIpcOpenMemHandle of rank %d: %s (use the NCCL route: dm_stats_snapshot / "
+                  "dm_stats_commit)", r, cudaGetErrorString(e));
+    }
+    h->peer_comm[r] = (PeerComm*)p;
+  }
+  h->peer_world = world;
+  return DM_OK;
+}
+
+extern "C" int dm_stats_allreduce(dm_handle* h, void* stream) {
+  if (!h) return fail(nullptr, DM_E_ARG, "dm_stats_allreduce: NULL handle");
+  int rc = peer_ensure(h);
+  if (rc) return rc;
+  CU(h, cudaSetDevice(h->device));
+  if (h->coll_stream) {  // exchanges are numbered: one issued by the caller goes behind those of the auto mode
+    CU(h, cudaEventRecord(h->coll_event, h->coll_stream));
+    CU(h, cudaStreamWaitEvent((cudaStream_t)stream, h->coll_event, 0));
+  }
+  return issue_exchange(h, (cudaStream_t)stream);
+}
+
+static PeerParams peer_params(const dm_handle* h, int enable) {
+  PeerParams p{};
+  p.acc = h->d_stats; p.snap = h->d_snap; p.total = h->d_total; p.st = h->d_peer_state;
+  for (int r = 0; r < kPeerMaxWorld; ++r) p.comm[r] = h->peer_comm[r];
+  p.rank = h->peer_rank; p.world = h->peer_world; p.n = h->dims.n_stats; p.enable = enable;
+  return p;
+}
+
+static int issue_exchange(dm_handle* h, cudaStream_t stream) {
+  stats_exchange_kernel<<<1, kPeerStride, 0, stream>>>(peer_params(h, 0));
+  CU(h, cudaGetLastError());
+  h->launches++;
+  return DM_OK;
+}
+
+extern "C" int dm_stats_set_auto(dm_handle* h, int32_t every) {
+  if (!h || every < 0) return fail(h, DM_E_ARG, "dm_stats_set_auto: every must be >= 0");
+  int rc = peer_ensure(h);
+  if (rc) return rc;
+  CU(h, cudaSetDevice(h->device));
+  if (every > 0 && !h->coll_stream) {
+    CU(h, cudaStreamCreateWithFlags(&h->coll_stream, cudaStreamNonBlocking));
+    CU(h, cudaEventCreateWithFlags(&h->coll_event, cudaEventDisableTiming));
+  }
+  h->auto_every = every;
+  h->auto_count = 0;
+  return DM_OK;
+}
+
+// `stream` waits for every exchange issued so far (the auto mode's side stream): call it before reading the totals on
+// `stream`, before timing marks, before dm_stats_zero
+extern "C" int dm_stats_join(dm_handle* h, void* stream) {
+  if (!h) return fail(nullptr, DM_E_ARG, "dm_stats_join: NULL handle");
+  if (!h->coll_stream) return DM_OK;
+  CU(h, cudaSetDevice(h->device));
+  CU(h, cudaEventRecord(h->coll_event, h->coll_stream));
+  CU(h, cudaStreamWaitEvent((cudaStream_t)stream, h->coll_event, 0));
+  return DM_OK;
+}
+
+extern "C" int dm_stats_snapshot(dm_handle* h, double** snapshot_dev_ptr, void* stream) {
+  if (!h) return fail(nullptr, DM_E_ARG, "dm_stats_snapshot: NULL handle");
+  int rc = peer_ensure(h);
+  if (rc) return rc;
+  CU(h, cudaSetDevice(h->device));
+  stats_snapshot_kernel<<<1, kPeerStride, 0, (cudaStream_t)stream>>>(h->d_stats, h->d_snap, h->dims.n_stats);
+  CU(h, cudaGetLastError());
+  h->launches++;
+  if (snapshot_dev_ptr) *snapshot_dev_ptr = h->d_snap;
+  return DM_OK;
+}
+
+extern "C" int dm_stats_commit(dm_handle* h, void* stream) {
+  if (!h || !h->d_total) return fail(h, DM_E_STATE, "dm_stats_commit: no snapshot (call dm_stats_snapshot first)");
+  CU(h, cudaSetDevice(h->device));
+  stats_commit_kernel<<<1, kPeerStride, 0, (cudaStream_t)stream>>>(h->d_snap, h->d_total, h->dims.n_stats);
+  CU(h, cudaGetLastError());
+  h->launches++;
+  return DM_OK;
+}
+
+extern "C" int dm_stats_read_total(dm_handle* h, double* host_out, void* stream) {
+  if (!h || !host_out) return fail(h, DM_E_ARG, "dm_stats_read_total: NULL argument");
+  int rc = peer_ensure(h);
+  if (rc) return rc;
+  CU(h, cudaSetDevice(h->device));
+  unsigned int err = 0;
+  if (h->coll_stream) CU(h, cudaStreamSynchronize(h->coll_stream));
+  CU(h, cudaMemcpyAsync(host_out, h->d_total, sizeof(double) * h->dims.n_stats, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  CU(h, cudaMemcpyAsync(&err, &h->d_peer_state->err, sizeof err, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  CU(h, cudaStreamSynchronize((cudaStream_t)stream));
+  if (err) return fail(h, DM_E_STATE, "dm_stats_read_total: a rank did not reach dm_stats_allreduce within %.1f s; the totals lack its share",
+                       kPeerTimeoutNs * 1e-9);
   return DM_OK;
 }

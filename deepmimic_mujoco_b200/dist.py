@@ -46,7 +46,9 @@ class _DevArray:
 
 
 def stats_tensor(hotpath):
-    """torch float64 tensor ALIASING the handle's device accumulators (no copy)."""
+    """torch float64 tensor ALIASING the handle's RUNNING device accumulators (no copy).  Never all-reduce this tensor in
+    place: the step kernels keep adding into it, so every further collective would multiply what was already summed
+    (round 1's bug: count 1.95e97 after 200 steps).  Use StatsCollective."""
     import torch
     ptr, n = hotpath.stats_device_ptr()
     return torch.as_tensor(_DevArray(ptr, n), device=torch.device("cuda", hotpath.device))
@@ -58,6 +60,82 @@ def allreduce_(t):
     if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
     return t
+
+
+def snapshot_allreduce_(acc, total):
+    """The protocol of the collective on plain torch tensors (any backend; the CPU / gloo tests run this):
+    snapshot-and-zero the running sums, all-reduce the SNAPSHOT, add it to the global totals."""
+    snap = acc.clone()
+    acc.zero_()
+    allreduce_(snap)
+    total += snap
+    return total
+
+
+class StatsCollective:
+    """The one collective of the path for a HotPath handle per rank.
+
+    mode "peer"  : dm_stats_allreduce -- one single-CTA kernel per call that exchanges the snapshot through peer-mapped
+                   memory over NVLink (csrc/dm_peer.cuh); no host-enqueued collective in the step loop.
+    mode "nccl"  : checked fallback when the cudaIpc mapping is not available: dm_stats_snapshot, ncclAllReduce of the
+                   snapshot through torch.distributed, dm_stats_commit.
+    mode "local" : world size 1.
+    Every rank must call reduce() the same number of times.  totals() = global running sums since the last stats_zero()."""
+
+    def __init__(self, hotpath, force_nccl=False):
+        import torch
+        import torch.distributed as dist
+        from . import _native as N
+        self.hp = hotpath
+        self.world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+        self.rank = dist.get_rank() if self.world > 1 else 0
+        self.mode = "local"
+        self.why_not_peer = None
+        if self.world > 1:
+            ok = 0 if force_nccl else 1
+            handle = b"\0" * N.IPC_HANDLE_BYTES
+            if ok:
+                try:
+                    handle = hotpath.stats_peer_export(self.rank, self.world)
+                except N.DmError as e:
+                    ok, self.why_not_peer = 0, str(e)
+            gathered = [None] * self.world
+            dist.all_gather_object(gathered, (ok, handle))
+            if all(g[0] for g in gathered):
+                try:
+                    hotpath.stats_peer_import([g[1] for g in gathered])
+                except N.DmError as e:
+                    ok, self.why_not_peer = 0, str(e)
+            else:
+                ok = 0
+            flag = torch.tensor([ok], device=torch.device("cuda", hotpath.device), dtype=torch.int32)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)  # every rank takes the same route
+            self.mode = "peer" if int(flag.item()) == 1 else "nccl"
+            if self.mode == "nccl":
+                ptr, n = hotpath.stats_snapshot()
+                self._snap = torch.as_tensor(_DevArray(ptr, n), device=torch.device("cuda", hotpath.device))
+
+    def reduce(self):
+        if self.mode == "nccl":
+            self.hp.stats_snapshot()
+            allreduce_(self._snap)
+            self.hp.stats_commit()
+        else:
+            self.hp.stats_allreduce()
+
+    def auto(self, every):
+        """Let dm_step issue the exchange itself (side stream, overlapping the next step).  Only the device-side routes can
+        do that; returns False in "nccl" mode, where the caller keeps calling reduce()."""
+        if self.mode == "nccl":
+            return False
+        self.hp.stats_set_auto(every)
+        return True
+
+    def join(self):
+        self.hp.stats_join()
+
+    def totals(self):
+        return self.hp.stats_read_total()
 
 
 def moments(stats, obs_dim):

@@ -323,6 +323,58 @@ class HotPath:
         N.check(self.L.dm_stats_device_ptr(self.h, C.byref(p), C.byref(n)), self.h, "dm_stats_device_ptr")
         return p.value, n.value
 
+    # the collective (include/dmhot.h: dm_stats_allreduce)
+    def stats_peer_export(self, rank, world):
+        buf = C.create_string_buffer(N.IPC_HANDLE_BYTES)
+        N.check(self.L.dm_stats_peer_export(self.h, int(rank), int(world), buf), self.h, "dm_stats_peer_export")
+        return buf.raw
+
+    def stats_peer_import(self, handles):
+        """handles: the `world` exported handles in rank order (bytes objects)."""
+        blob = b"".join(handles)
+        N.check(self.L.dm_stats_peer_import(self.h, len(handles), C.c_char_p(blob)), self.h, "dm_stats_peer_import")
+
+    def stats_allreduce(self, stream=None):
+        """Snapshot-and-zero this rank's sums, exchange with the other ranks on the device, add to the global totals."""
+        if stream is None:
+            import torch
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        rc = self.L.dm_stats_allreduce(self.h, stream)
+        if rc:
+            N.check(rc, self.h, "dm_stats_allreduce")
+
+    def stats_snapshot(self, stream=None):
+        """Fallback route, step 1: acc -> snapshot (zeroing acc); returns (device pointer, n) of the snapshot."""
+        if stream is None:
+            import torch
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        p = C.c_void_p()
+        N.check(self.L.dm_stats_snapshot(self.h, C.byref(p), stream), self.h, "dm_stats_snapshot")
+        return p.value, self.dims.n_stats
+
+    def stats_commit(self, stream=None):
+        """Fallback route, step 3 (after the all-reduce of the snapshot): totals += snapshot."""
+        if stream is None:
+            import torch
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        N.check(self.L.dm_stats_commit(self.h, stream), self.h, "dm_stats_commit")
+
+    def stats_set_auto(self, every):
+        """every > 0: dm_step issues the exchange itself behind every `every`-th step with statistics, on a side stream."""
+        N.check(self.L.dm_stats_set_auto(self.h, int(every)), self.h, "dm_stats_set_auto")
+
+    def stats_join(self, stream=None):
+        """Make `stream` wait for every exchange issued so far."""
+        if stream is None:
+            import torch
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        N.check(self.L.dm_stats_join(self.h, stream), self.h, "dm_stats_join")
+
+    def stats_read_total(self, stream=None):
+        out = np.zeros(self.dims.n_stats)
+        N.check(self.L.dm_stats_read_total(self.h, N.np_ptr(out), stream), self.h, "dm_stats_read_total")
+        return out
+
     def launch_count(self):
         k = C.c_int64()
         N.check(self.L.dm_launch_count(self.h, C.byref(k)), self.h, "dm_launch_count")

@@ -204,6 +204,39 @@ int dm_stats_zero(dm_handle* h, void* stream);
 int dm_stats_device_ptr(dm_handle* h, double** dev_ptr, int32_t* n); /* for an in-place NCCL all-reduce */
 int dm_stats_read(dm_handle* h, double* host_out, void* stream);
 
+/* The collective of the path (the reference has none: SubprocVecEnv pipes only, src/sb3_ppo.py:275-278).
+ * One process per GPU, every rank owns a contiguous block of environments and its own handle.  The step kernels add
+ * into the rank's accumulators; dm_stats_allreduce SNAPSHOTS-AND-ZEROES them, exchanges the snapshot with every other
+ * rank and adds the sum (taken in rank order: the same bits on every rank) to the handle's GLOBAL TOTALS, which
+ * dm_stats_read_total returns and dm_policy_normalizer_from_stats uses from then on.  Only snapshots are ever reduced,
+ * never running sums.  The exchange is ONE single-CTA kernel on `stream` that writes into the other GPUs' memory over
+ * NVLink (cudaIpc peer mappings) and waits on flags there: no host round trip, no NCCL launch, capturable in a CUDA graph.
+ * Every rank must call it the same number of times; a rank that waits longer than 2 s for a peer gives up and
+ * dm_stats_read_total then fails with DM_E_STATE.  With one rank (no dm_stats_peer_import) it is the local
+ * snapshot -> totals move.  dm_stats_zero also clears the snapshot and the totals.
+ *   set-up, once:  dm_stats_peer_export(h, rank, world, handle[DM_IPC_HANDLE_BYTES])  -> all-gather the handles by any
+ *                  means (the launcher's process group, MPI, a file) -> dm_stats_peer_import(h, world, handles[world][64]) on every rank.
+ *   fallback where cudaIpc is not available (dm_stats_peer_import fails): dm_stats_snapshot(h, &dev_ptr, stream),
+ *                  ncclAllReduce(dev_ptr, n_stats doubles, sum), dm_stats_commit(h, stream). */
+#define DM_IPC_HANDLE_BYTES 64
+int dm_stats_peer_export(dm_handle* h, int32_t rank, int32_t world, void* handle_out);
+int dm_stats_peer_import(dm_handle* h, int32_t world, const void* handles);
+int dm_stats_allreduce(dm_handle* h, void* stream);
+int dm_stats_snapshot(dm_handle* h, double** snapshot_dev_ptr, void* stream);
+int dm_stats_commit(dm_handle* h, void* stream);
+int dm_stats_read_total(dm_handle* h, double* host_out, void* stream);
+/* Auto mode: every `every`-th dm_step with accumulate_stats = 1 carries an exchange itself (0 = off).  Where the tile
+ * kernel runs (row-major batches of >= 128 environments, the normal case) the exchange is ONE EXTRA CTA of that kernel:
+ * once the previous step is complete it collects the exchange posted one step earlier -- whose data has had a whole
+ * step to cross NVLink -- and posts the sums accumulated since; no extra launch, no event, no exposed latency.  The
+ * global totals therefore trail the steps by up to two exchanges while the loop runs; one dm_stats_allreduce after the
+ * last step collects what is pending and exchanges the remainder, after which dm_stats_read_total is exact.  Snapshots
+ * are taken atomically, so no contribution is ever lost or counted twice.  Other launch shapes fall back to the
+ * exchange kernel on a side stream owned by the handle, ordered behind the step by an event.
+ * dm_stats_join makes `stream` wait for every exchange issued on that side stream so far. */
+int dm_stats_set_auto(dm_handle* h, int32_t every);
+int dm_stats_join(dm_handle* h, void* stream);
+
 /* dm_batch_stats_noalloc -- NO COUNTERPART IN THE REFERENCE.
  * The same statistics vector as above for ONE batch, computed without any allocation: no cudaMalloc, cudaFree or
  * allocating library routine is called, so it can be used where those are forbidden (CUDA graph capture, tight serving

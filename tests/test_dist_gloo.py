@@ -52,7 +52,19 @@ def _worker(rank, world, port, q):
         dmdist.allreduce_(t)
         last = t.numpy().copy()
         norm.update_from_sums(last[0], last[6:6 + D], last[6 + D:])
-    q.put((rank, last, norm.mean, norm.var, norm.n))
+    # the collective's protocol on a RUNNING accumulator (reducing the running sums in place multiplied
+    # them): four step -> reduce cycles, two of them with two steps between the reductions
+    acc, total = torch.zeros(6 + 2 * D, dtype=torch.float64), torch.zeros(6 + 2 * D, dtype=torch.float64)
+    step = 0
+    for steps_between in (1, 2, 1, 2):
+        for _ in range(steps_between):
+            full = _batch(step)
+            lo, hi = dmdist.shard(len(full[1]), rank, world)
+            acc += torch.from_numpy(_sums(*[a[lo:hi] for a in full]))
+            step += 1
+        dmdist.snapshot_allreduce_(acc, total)
+        assert not acc.any()
+    q.put((rank, last, norm.mean, norm.var, norm.n, total.numpy().copy(), step))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -86,6 +98,12 @@ def test_two_rank_statistics_allreduce():
         np.testing.assert_allclose(r[3], allobs.var(0), rtol=1e-9)
         assert r[4] == len(allobs)
     np.testing.assert_array_equal(res[0][2], res[1][2])
+    # running totals after four reductions == float64 numpy over every batch of every rank; the count is exact
+    want = sum(_sums(*_batch(s)) for s in range(res[0][6]))
+    for r in res:
+        assert r[5][0] == want[0] == sum(len(_batch(s)[1]) for s in range(res[0][6]))
+        np.testing.assert_allclose(r[5], want, rtol=1e-12)
+    np.testing.assert_array_equal(res[0][5], res[1][5])
     m = dmdist.moments(res[0][1], D)
     np.testing.assert_allclose(m["reward_mean"], full[1].mean(), rtol=1e-12)
     np.testing.assert_allclose(m["done_rate"], full[2].mean(), rtol=1e-12)
