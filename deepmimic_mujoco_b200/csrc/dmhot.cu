@@ -15,6 +15,7 @@
 #include "dm_kernels.cuh"
 #include "dm_tile_launch.cuh"
 #include "dm_team_launch.cuh"
+#include "dm_soa_kernel.cuh"
 #include "dm_pack.h"
 #include <chrono>
 #include "dm_copy_pool.h"
@@ -54,6 +55,8 @@ struct dm_handle {
   int peer_rank = 0, peer_world = 1;        // world 1 until dm_stats_peer_import has connected the ranks
   int auto_every = 0;                       // dm_stats_set_auto: an exchange with every auto_every-th dm_step with statistics
   long long auto_count = 0;
+  struct SoaMapEntry { const void *q, *v, *o; long long ld; int n; SoaMaps maps; };
+  std::vector<SoaMapEntry> soa_maps;  // tensor maps of the SoA buffer sets seen lately (encoding costs a few us per call)
   bool fuse_now = false, fused_done = false;  // this dm_step is due an exchange / the tile kernel carried it (exchange CTA)
   cudaStream_t coll_stream = nullptr;       // side stream of the auto mode
   cudaEvent_t coll_event = nullptr;
@@ -458,6 +461,29 @@ static T* off(T* p, long long n) { return p ? p + n : p; }
 
 static PeerParams peer_params(const dm_handle* h, int enable);
 
+// 2-D tensor map of a row-major [rows, ld] fp32 array whose boxes are `box_rows` rows of 128 consecutive environments
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static int soa_encode(dm_handle* h, CUtensorMap* tm, const float* base, int rows, long long ld, int n, int box_rows) {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) != cudaSuccess || !p)
+      return fail(h, DM_E_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    fn = (EncodeTiledFn)p;
+  }
+  const cuuint64_t dims[2] = {(cuuint64_t)n, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(float)};
+  const cuuint32_t box[2] = {128u, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1u, 1u};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(h, DM_E_CUDA, "cuTensorMapEncodeTiled failed (%d) for a [%d, %lld] array", (int)r, rows, ld);
+  return DM_OK;
+}
+
 static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
   if (a->n == 0) return DM_OK;
   return dispatch(h, [&](auto rb, auto kind) -> int {
@@ -480,6 +506,7 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
                            reinterpret_cast<uintptr_t>(a->obs) | reinterpret_cast<uintptr_t>(a->action) |
                            reinterpret_cast<uintptr_t>(a->torque)) & 15u) == 0;
     int tiled = 0;
+    bool soa_tiled = false;
     const bool team = h->variant == 2;
     if (p.aos && team && aligned && a->n >= 32) {
       // K1c: tiles of 32 environments, one team of four warps per tile (dm_team_kernel.cuh)
@@ -523,10 +550,51 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
     } else if (p.aos && !team && h->variant != 0 && aligned && a->n >= TC::TE) {
       tiled = a->n / TC::TE * TC::TE;
       timing_begin(h, s);
+    } else if (!p.aos && h->variant != 0 && aligned && a->ld % 4 == 0 && a->n >= 128) {
+      // K1s: structure-of-arrays batches, tiles of 128 environments as one 512-byte bulk copy per row (dm_soa_kernel.cuh)
+      using SC = SoaCfg<KIND, Rb>;
+      tiled = a->n / SC::TE * SC::TE;
+      soa_tiled = true;
+      const int n_tiles = tiled / SC::TE;
+      const size_t table_bytes = sizeof(float) * (size_t)h->total_rows * RowLayout<Rb>::STRIDE;
+      const size_t acc_bytes = a->accumulate_stats ? SC::ACC_BYTES : 0;
+      const size_t avail = SC::SMEM_BUDGET - SC::FIXED_BYTES;
+      int G = SoaGroups<Rb>::G;
+      while (G > 1 && G * (SC::SLOT_BYTES + acc_bytes) > avail) --G;
+      const int want = (n_tiles + h->num_sms - 1) / h->num_sms;
+      G = want < G ? (want < 1 ? 1 : want) : G;
+      const size_t table_pad = (table_bytes + 127) / 128 * 128;  // tensor-map copies want 128-byte aligned shared memory
+      bool table_smem = table_pad + G * (SC::SLOT_BYTES + acc_bytes) <= avail;
+      if (h->table_smem_override >= 0) table_smem = table_smem && h->table_smem_override != 0;
+      const size_t smem = SC::FIXED_BYTES + (table_smem ? table_pad : 0) + G * (SC::SLOT_BYTES + acc_bytes);
+      const int grid = (n_tiles + G - 1) / G < h->num_sms ? (n_tiles + G - 1) / G : h->num_sms;
+      StepParams q = p;
+      q.n = tiled;
+      SoaExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float)), (int)(table_pad / sizeof(float))};
+      const SoaMaps* maps = nullptr;
+      for (const auto& m : h->soa_maps)
+        if (m.q == a->qpos && m.v == a->qvel && m.o == a->obs && m.ld == a->ld && m.n == tiled) { maps = &m.maps; break; }
+      if (!maps) {
+        if (h->soa_maps.size() >= 128) h->soa_maps.clear();
+        h->soa_maps.reserve(128);  // entries never move while they are referenced below
+        dm_handle::SoaMapEntry m{a->qpos, a->qvel, a->obs, a->ld, tiled, {}};
+        int rc2 = soa_encode(h, &m.maps.q, a->qpos, Rb::NQ, a->ld, tiled, Rb::NQ);
+        if (!rc2) rc2 = soa_encode(h, &m.maps.v, a->qvel, Rb::NV, a->ld, tiled, Rb::NV);
+        if (!rc2) rc2 = soa_encode(h, &m.maps.oj, a->obs, OL::DIM, a->ld, tiled, Rb::NJ);
+        if (!rc2) rc2 = soa_encode(h, &m.maps.oc, a->obs, OL::DIM, a->ld, tiled, SC::NCOMP);
+        if (rc2) return rc2;
+        h->soa_maps.push_back(m);
+        maps = &h->soa_maps.back().maps;
+      }
+      SoaLaunch sl{grid, G, smem, s, h->pdl != 0, a->terms != nullptr, a->accumulate_stats != 0, table_smem, maps};
+      timing_begin(h, s);
+      cudaError_t e = launch_soa<KIND, Rb>(sl, q, ex);
+      CU(h, e);
+      h->launches++;
     } else {
       timing_begin(h, s);
     }
-    if (tiled && !team) {
+    if (tiled && !team && !soa_tiled) {
       StepParams q = p;
       q.n = tiled;
       constexpr int GMAX = KernelGroups<Rb>::G;
@@ -595,7 +663,12 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
     if (rest) {
       StepParams q = p;
       q.n = rest;
-      if (tiled) {  // only reachable for AoS
+      if (tiled && soa_tiled) {  // SoA: the tail starts `tiled` environments into every row
+        q.qpos = off(p.qpos, tiled); q.qvel = off(p.qvel, tiled); q.action = off(p.action, tiled); q.contact = off(p.contact, tiled);
+        q.idx = off(p.idx, tiled); q.ep_len = off(p.ep_len, tiled); q.clip = off(p.clip, tiled);
+        q.obs = off(p.obs, tiled); q.reward = off(p.reward, tiled); q.done = off(p.done, tiled); q.reason = off(p.reason, tiled);
+        q.torque = off(p.torque, tiled); q.terms = off(p.terms, tiled); q.ep_return = off(p.ep_return, tiled);
+      } else if (tiled) {  // AoS
         q.qpos = off(p.qpos, (long long)tiled * Rb::NQ); q.qvel = off(p.qvel, (long long)tiled * Rb::NV);
         q.action = off(p.action, (long long)tiled * Rb::NA); q.contact = off(p.contact, tiled);
         q.idx = off(p.idx, tiled); q.ep_len = off(p.ep_len, tiled); q.clip = off(p.clip, tiled);
