@@ -28,12 +28,21 @@ BYTES_PER_ENV_STEP = {("humanoid3d", 0): 793, ("unitree_g1", 0): 953, ("unitree_
 L2_BYTES = 126e6
 STATE_SEED = 1234  # rank r's headline batches: synth_states(..., seed = STATE_SEED + r) on the CPU generator
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE step-kernel launch from `ncu --set full` captures of this very
-# command (profiles/r01_step_tile_s18_*_ncu_full_summary.txt), keyed by (robot, env kind, envs per GPU); at 4096 envs the
-# 1.7 MB of outputs are still dirty in L2 when the kernel ends, so only the reads reach DRAM inside the launch
-NCU_TRAFFIC = {("humanoid3d", 0, 4096): (1.764096e6, "profiles/r01_step_tile_s18_h4096_ncu_full_summary.txt"),
-               ("humanoid3d", 0, 1048576): (427.913216e6 + 362.767616e6, "profiles/r01_step_tile_s18_h1M_ncu_full_summary.txt"),
-               ("unitree_g1", 1, 1048576): (484.756480e6 + 535.972096e6, "profiles/r01_step_tile_s18_g1c_1M_ncu_full_summary.txt"),
-               ("unitree_g1", 1, 262144): (120.824832e6 + 95.611392e6, "profiles/r01_step_tile_s18_g1c_262144_ncu_full_summary.txt")}
+# shape (tools/gpu_r2_ncu_all.sh -> profiles/r02_*_ncu_full_summary.txt), keyed by (robot, env kind, envs per GPU, layout).
+# Small batches: the outputs are still dirty in L2 when the kernel ends, so only the reads reach DRAM inside the launch.
+def _t(name, rd, wr):
+    return (rd + wr, "profiles/r02_%s_ncu_full_summary.txt" % name)
+
+
+NCU_TRAFFIC = {("humanoid3d", 0, 4096, "aos"): _t("h4096", 1.769472e6, 0.0),
+               ("humanoid3d", 0, 8192, "aos"): _t("c3_8192", 3.487744e6, 0.0),
+               ("humanoid3d", 0, 65536, "aos"): _t("c3_65536", 26.884608e6, 0.460544e6),
+               ("humanoid3d", 0, 1048576, "aos"): _t("h1M", 427.973120e6, 364.157952e6),
+               ("unitree_g1", 1, 32768, "aos"): _t("g1c_32768", 15.309824e6, 0.0),
+               ("unitree_g1", 1, 262144, "aos"): _t("g1c_262144", 120.824576e6, 97.478656e6),
+               ("unitree_g1", 1, 1048576, "aos"): _t("g1c_1M", 482.838528e6, 534.682112e6),
+               ("humanoid3d", 0, 1048576, "soa"): _t("soa_h1M", 428.956928e6, 366.176256e6),
+               ("unitree_g1", 1, 1048576, "soa"): _t("soa_g1c_1M", 482.617344e6, 535.082752e6)}
 
 
 def parse():
@@ -620,7 +629,7 @@ def run_config(args, device, rank, world, envs_per_rank, steps, warmup, seed, wi
     k_ms, _ = kernel_time(wl, min(steps, 50))
     gbs = wl.bpe * envs_per_rank / (k_ms * 1e-3) / 1e9
     out.update(kernel_ms=k_ms, GBps=gbs, frac=gbs / peak, bytes_per_env_step=wl.bpe)
-    tr = NCU_TRAFFIC.get((wl.hp.robot, wl.kind, envs_per_rank))
+    tr = NCU_TRAFFIC.get((wl.hp.robot, wl.kind, envs_per_rank, args.layout))
     if tr:
         out["traffic"], out["traffic_source"] = tr
     wl.hp.close()
@@ -651,8 +660,8 @@ def configs_block(args, device, rank, world, peak):
         sweep.append(row)
     blk["config5_sweep"] = sweep
     if args.layout == "aos":  # the SoA layout at 1 M environments next to the row-major one
-        so = _variant_args(h1, layout="soa")
-        blk["layout_soa_humanoid3d_walk_1M"] = run_config(so, device, rank, world, 1 << 20, 10, 3, 700, False, peak)
+        blk["layout_soa_humanoid3d_walk_1M"] = run_config(_variant_args(h1, layout="soa"), device, rank, world, 1 << 20, 10, 3, 700, False, peak)
+        blk["layout_soa_g1_combined_1M"] = run_config(_variant_args(c4, layout="soa"), device, rank, world, 1 << 20, 10, 3, 710, False, peak)
     return blk
 
 
@@ -691,8 +700,8 @@ def main():
     bytes_per_launch = wl.bpe * args.envs
     ach = bytes_per_launch / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
     roof = {"bound": "hbm", "kernel": "step kernel (K1)", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-            "traffic": NCU_TRAFFIC.get((wl.hp.robot, wl.kind, args.envs), (None, None))[0],
-            "traffic_source": NCU_TRAFFIC.get((wl.hp.robot, wl.kind, args.envs), (None, None))[1], "peak_source": peak_src, "bytes_per_env_step": wl.bpe, "envs_per_launch": args.envs,
+            "traffic": NCU_TRAFFIC.get((wl.hp.robot, wl.kind, args.envs, args.layout), (None, None))[0],
+            "traffic_source": NCU_TRAFFIC.get((wl.hp.robot, wl.kind, args.envs, args.layout), (None, None))[1], "peak_source": peak_src, "bytes_per_env_step": wl.bpe, "envs_per_launch": args.envs,
             "kernel_ms": k_ms, "kernel_launches_timed": k_n}
 
     line = {"metric": "env-steps/s (ref-lookup+FK+reward+obs+PD)", "value": value, "unit": "env-steps/s", "n_gpus": world,

@@ -32,11 +32,11 @@ struct SoaCfg {
   static constexpr int TE = 128, NW = TE / 32;
   static constexpr int NCOMP = OL::DIM - 2 * Rb::NJ;         // computed observation rows
   static constexpr int IN_ROWS = Rb::NQ + Rb::NV;            // staged rows of one input tile (actions are read directly)
-  static constexpr int SLOT_ROWS = IN_ROWS + NCOMP + 1;      // + computed rows + the reward row (statistics)
+  static constexpr int SLOT_ROWS = IN_ROWS + NCOMP;          // + computed rows (the tile's rewards reuse qpos row 0, dead by then)
   static constexpr int SLOT_FLOATS = SLOT_ROWS * TE;
   static constexpr size_t SLOT_BYTES = sizeof(float) * SLOT_FLOATS;
   static constexpr int NCOLS = OL::DIM + 1;                  // statistics columns: observation entries, then the reward
-  static constexpr size_t ACC_BYTES = sizeof(double) * (2 * NCOLS + 4);  // per group
+  static constexpr size_t ACC_BYTES = sizeof(double) * (2 * NCOLS + 4);  // per CTA (shared-memory fp64 atomics)
   static constexpr int MAXG = 4;
   static constexpr size_t FIXED_BYTES = 128;                 // mbarriers: [0, MAXG) slots, [MAXG] table
   static constexpr size_t SMEM_BUDGET = 227 * 1024;
@@ -87,8 +87,10 @@ struct SoaIO {
 
 // groups per CTA the kernel is compiled for (register budget = 65536 / (128 G) per thread); SoA needs fewer registers
 // than K1b: no joint blocks or computed entries are held across the tile barrier
-template <class Rb> struct SoaGroups { static constexpr int G = 4; };
-template <> struct SoaGroups<Robot_unitree_g1> { static constexpr int G = 3; };
+template <int KIND, class Rb> struct SoaGroups { static constexpr int G = 4; };
+// measured at 1 M / 262 144 envs: unitree_g1 DPEnv 272 us with four groups (128 registers, no spills) against 287 with three;
+// the combined env 300 / 94.5 us with four against 298 / 83.5 with three (its 57 KB slots leave the fourth group no slack)
+template <> struct SoaGroups<KIND_COMBINED, Robot_unitree_g1> { static constexpr int G = 3; };
 
 template <int KIND, class Rb, bool TERMS, bool STATS, bool TABLE_SMEM, int G>
 __global__ void __launch_bounds__(128 * G, 1) step_soa_kernel(const __grid_constant__ StepParams p, const SoaExtra x,
@@ -106,9 +108,8 @@ __global__ void __launch_bounds__(128 * G, 1) step_soa_kernel(const __grid_const
   float* s_q = slot;                       // [NQ][TE]
   float* s_v = s_q + NQ * TE;              // [NV][TE]
   float* s_c = s_v + NV * TE;              // [NCOMP][TE] computed observation rows
-  float* s_rw = s_c + NCOMP * TE;          // [TE] rewards of the tile (statistics)
-  double* g_acc = reinterpret_cast<double*>(s_table + (TABLE_SMEM ? x.table_pad : 0) + (size_t)n_groups * SC::SLOT_FLOATS) +
-                  (size_t)group * (2 * SC::NCOLS + 4);
+  float* s_rw = s_q;                       // [TE] rewards of the tile (statistics): qpos row 0 (root x), dead after the step
+  double* g_acc = reinterpret_cast<double*>(s_table + (TABLE_SMEM ? x.table_pad : 0) + (size_t)n_groups * SC::SLOT_FLOATS);  // CTA-wide
   const long long ld = p.es;
   const bool want_tau = p.torque != nullptr;
   // this group's tiles: (j * grid + cta) * n_groups + group
@@ -127,7 +128,7 @@ __global__ void __launch_bounds__(128 * G, 1) step_soa_kernel(const __grid_const
     mbar_fence_init();
   }
   if (STATS) {
-    for (int k = gt; k < 2 * SC::NCOLS + 4; k += TE) g_acc[k] = 0.0;
+    for (int k = tid; k < 2 * SC::NCOLS + 4; k += blockDim.x) g_acc[k] = 0.0;
   }
   __syncthreads();
   if (TABLE_SMEM && tid == 0) {
@@ -241,9 +242,9 @@ __global__ void __launch_bounds__(128 * G, 1) step_soa_kernel(const __grid_const
         }
       }
       const int r = warp + SC::NW * lane;  // lane L holds row index L of this warp's list
-      if (lane < NI && r <= DIM) {
-        g_acc[r] += va[0];
-        g_acc[SC::NCOLS + r] += vb[0];
+      if (lane < NI && r <= DIM) {  // the groups of a CTA share one set of running sums
+        atomicAdd(g_acc + r, double(va[0]));
+        atomicAdd(g_acc + SC::NCOLS + r, double(vb[0]));
       }
     }
     if (gt == 0) bulk_wait_read0();  // the stores have read the slot
@@ -252,24 +253,17 @@ __global__ void __launch_bounds__(128 * G, 1) step_soa_kernel(const __grid_const
   }
 
   if (gt == 0) bulk_wait_read0();
-  if (STATS && x.acc) {  // one set of fp64 atomics per CTA
-    if (gt == 0) g_acc[2 * SC::NCOLS + 3] = double(nt);
+  if (STATS && x.acc) {  // one set of fp64 global atomics per CTA
+    if (gt == 0) atomicAdd(g_acc + 2 * SC::NCOLS + 3, double(nt));
     __syncthreads();
-    const double* acc0 = reinterpret_cast<const double*>(s_table + (TABLE_SMEM ? x.table_pad : 0) + (size_t)n_groups * SC::SLOT_FLOATS);
-    constexpr int GS = 2 * SC::NCOLS + 4;
-    auto over_groups = [&](int k) {
-      double v = 0.0;
-      for (int g = 0; g < n_groups; ++g) v += acc0[(size_t)g * GS + k];
-      return v;
-    };
     for (int k = tid; k < 2 * DIM + 6; k += blockDim.x) {
       double v;
-      if (k == 0) v = over_groups(2 * SC::NCOLS + 3) * TE;       // count
-      else if (k == 1) v = over_groups(DIM);                      // sum r
-      else if (k == 2) v = over_groups(SC::NCOLS + DIM);          // sum r^2
-      else if (k < 6) v = over_groups(2 * SC::NCOLS + k - 3);     // n_done, sum ep_return(done), sum ep_len(done)
-      else if (k < 6 + DIM) v = over_groups(k - 6);
-      else v = over_groups(SC::NCOLS + k - 6 - DIM);
+      if (k == 0) v = g_acc[2 * SC::NCOLS + 3] * TE;          // count
+      else if (k == 1) v = g_acc[DIM];                         // sum r
+      else if (k == 2) v = g_acc[SC::NCOLS + DIM];             // sum r^2
+      else if (k < 6) v = g_acc[2 * SC::NCOLS + k - 3];        // n_done, sum ep_return(done), sum ep_len(done)
+      else if (k < 6 + DIM) v = g_acc[k - 6];
+      else v = g_acc[SC::NCOLS + k - 6 - DIM];
       if (v != 0.0) atomicAdd(x.acc + k, v);
     }
   }
@@ -304,7 +298,7 @@ static cudaError_t launch_soa_impl(const SoaLaunch& c, const StepParams& q, cons
     cfg.numAttrs = c.pdl ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kern, q, ex, *c.maps);
   };
-  constexpr int GK = SoaGroups<Rb>::G;
+  constexpr int GK = SoaGroups<KIND, Rb>::G;
   auto pick = [&](auto terms, auto stats) -> cudaError_t {
     constexpr bool T = decltype(terms)::value, S = decltype(stats)::value;
     return c.table_smem ? launch(step_soa_kernel<KIND, Rb, T, S, true, GK>) : launch(step_soa_kernel<KIND, Rb, T, S, false, GK>);

@@ -559,14 +559,14 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
       const size_t table_bytes = sizeof(float) * (size_t)h->total_rows * RowLayout<Rb>::STRIDE;
       const size_t acc_bytes = a->accumulate_stats ? SC::ACC_BYTES : 0;
       const size_t avail = SC::SMEM_BUDGET - SC::FIXED_BYTES;
-      int G = SoaGroups<Rb>::G;
-      while (G > 1 && G * (SC::SLOT_BYTES + acc_bytes) > avail) --G;
+      int G = SoaGroups<KIND, Rb>::G;
+      while (G > 1 && G * SC::SLOT_BYTES + acc_bytes > avail) --G;
       const int want = (n_tiles + h->num_sms - 1) / h->num_sms;
       G = want < G ? (want < 1 ? 1 : want) : G;
       const size_t table_pad = (table_bytes + 127) / 128 * 128;  // tensor-map copies want 128-byte aligned shared memory
-      bool table_smem = table_pad + G * (SC::SLOT_BYTES + acc_bytes) <= avail;
+      bool table_smem = table_pad + G * SC::SLOT_BYTES + acc_bytes <= avail;
       if (h->table_smem_override >= 0) table_smem = table_smem && h->table_smem_override != 0;
-      const size_t smem = SC::FIXED_BYTES + (table_smem ? table_pad : 0) + G * (SC::SLOT_BYTES + acc_bytes);
+      const size_t smem = SC::FIXED_BYTES + (table_smem ? table_pad : 0) + G * SC::SLOT_BYTES + acc_bytes;
       const int grid = (n_tiles + G - 1) / G < h->num_sms ? (n_tiles + G - 1) / G : h->num_sms;
       StepParams q = p;
       q.n = tiled;
