@@ -359,7 +359,8 @@ def e2e_region(args, steps, warmup, seed, local_rank=0, world=1):
     HOST numpy buffers: H2D of the step's inputs, kernel, D2H of obs / reward / done / torque every step."""
     import torch
     from deepmimic_mujoco_b200.vec_env import DPVecEnv
-    env = DPVecEnv(args.envs, motion=args.motion.split(","), robot=args.robot, combined=args.combined, seed=seed, device=local_rank)
+    env = DPVecEnv(args.envs, motion=args.motion.split(","), robot=args.robot, combined=args.combined, seed=seed, device=local_rank,
+                   pin_cpus="auto" if world > 1 else None)
     dev = torch.device("cuda", local_rank)
     B = 8
     s = synth_states(env.hp, args.envs, B, seed + 1, dev)
@@ -394,7 +395,8 @@ def e2e_region(args, steps, warmup, seed, local_rank=0, world=1):
     torch.cuda.synchronize()
     dt = over_ranks(time.perf_counter() - t0)
     assert obs.shape == (args.envs, env.hp.obs_dim) and len(infos) == args.envs
-    out = dict(value=world * args.envs * steps / dt, unit="env-steps/s", h2d_bytes_per_step=int(env.h2d_bytes) * world,
+    out = dict(value=world * args.envs * steps / dt, unit="env-steps/s", cpus_per_rank=None if env.cpus is None else len(env.cpus),
+               h2d_bytes_per_step=int(env.h2d_bytes) * world,
                d2h_bytes_per_step=int(env.d2h_bytes) * world, ms_per_step=1e3 * dt / steps,
                api="DPVecEnv.step(actions, force_state=(qpos, qvel, contact)) with ordinary (pageable) numpy inputs and caller-owned "
                    "outputs: dm_step_host copies the inputs into the handle's pinned block in chunks of whole tiles (copies shared "

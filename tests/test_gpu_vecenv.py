@@ -89,7 +89,8 @@ def test_vecenv_pinned_inputs_are_zero_copy_and_equal():
     b.close()
 
 
-@pytest.mark.parametrize("n,combined,chunk", [(128, False, 0), (4096 + 37, False, 0), (2048 + 5, False, 256), (1024 + 3, True, 512)])
+@pytest.mark.parametrize("n,combined,chunk", [(128, False, 0), (4096 + 37, False, 0), (2048 + 5, False, 256), (1024 + 3, True, 512),
+                                              (262144, True, 0)])  # BASELINE configs[3] at full size through the host API
 def test_host_step_mapped_equals_staged(n, combined, chunk, monkeypatch):
     """dm_step_host on the pinned block directly (DM_HOST_MAPPED: the kernel's TMA copies cross PCIe, caller arrays staged
     in chunks of whole tiles over two streams) against the copy-engine form (DM_HOST_STAGED): the same kernel on other
