@@ -60,7 +60,7 @@ def parse():
     ap.add_argument("--allreduce-every", type=int, default=1, help="steps between two statistics collectives (N > 1); BASELINE "
                     "configs[2] asks for one EVERY step")
     ap.add_argument("--collective", default="auto", choices=["auto", "reduce", "nccl", "off"],
-                    help="auto: dm_step issues the device-side exchange itself on a side stream (overlaps the next step); reduce: "
+                    help="auto: dm_step issues the device-side lagged exchange itself (side stream or exchange CTA, dm_peer.cuh); reduce: "
                          "the same exchange launched explicitly between the steps; nccl: snapshot + ncclAllReduce + commit")
     ap.add_argument("--collective-at-1", action="store_true", help="run the collective's local form at N = 1 too (cost probe)")
     ap.add_argument("--no-configs", action="store_true", help="skip the BASELINE configs block (configs 3, 4, 5, 1 M row)")
@@ -245,6 +245,13 @@ class Workload:
                      self.ep_return[b], soa_ld=(self.n if self.soa else 0), stats=self.stats)
 
 
+def launch_gate_us(steps):
+    """Length of the device-side gate in front of a timed region: ~10 us per step queued, 100 us .. 2 ms."""
+    if "DM_BENCH_GATE_US" in os.environ:
+        return float(os.environ["DM_BENCH_GATE_US"])
+    return float(min(max(10 * steps, 100), 2000))
+
+
 def timed_region(wl, steps, warmup, world, every, coll, mode):
     """W untimed + exactly K timed steps, barrier + synchronize on both sides, CUDA events, max over ranks.
     coll: the statistics collective (deepmimic_mujoco_b200.dist.StatsCollective) or None; with `mode` "auto" dm_step issues
@@ -274,6 +281,13 @@ def timed_region(wl, steps, warmup, world, every, coll, mode):
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
+    # A short region (the driver's 20 steps of ~9 us) would otherwise start on an EMPTY launch queue and measure the host's
+    # launch ramp -- on every rank, coupled through the exchange -- rather than the device (N = 2, 20 steps: 232 us without,
+    # 194 us with the gate; 200 steps: 9.13 vs 9.11 us per step).  A device-side gate holds the stream while the host
+    # queues the region's launches; the events sit behind the gate.  DM_BENCH_GATE_US=0 switches it off.
+    gate_us = launch_gate_us(steps)
+    if gate_us > 0:
+        torch.cuda._sleep(int(gate_us * 2000))
     if coll is not None and world > 1 and not os.environ.get("DM_BENCH_NO_ALIGN"):
         # the host barrier releases the ranks tens of microseconds apart -- a tenth of a 20-step region at 4096 environments.
         # One exchange of (zeroed) statistics lines the GPUs up to within the NVLink round trip before the clock starts.
@@ -317,6 +331,9 @@ def kernel_time(wl, steps):
         wl.step()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    gate_us = launch_gate_us(steps)  # as in timed_region: the queue is filled before the first event
+    if gate_us > 0:
+        torch.cuda._sleep(int(gate_us * 2000))
     e0.record()
     for _ in range(steps):
         wl.step()
@@ -714,6 +731,8 @@ def main():
                        "l2_policy": "inputs larger than L2: %d distinct resident batches (%.0f MB) cycled" %
                                     (wl.B, wl.B * bytes_per_launch / 1e6),
                        "stats": wl.stats,
+                       "launch_queue": "the K step launches are queued behind a device-side gate of %.0f us (torch.cuda._sleep) in front of "
+                                       "the first event, so that the region times the device and not the host's launch ramp" % launch_gate_us(args.steps),
                        "collective": None if coll is None else {"mode": coll.mode, "issue": args.collective, "every": args.allreduce_every,
                                                                 "why_not_peer": coll.why_not_peer}},
             "roofline": roof, "gpu_launches": int(launches), "clocks": clocks}

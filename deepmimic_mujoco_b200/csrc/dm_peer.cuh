@@ -5,20 +5,30 @@
 // ncclAllReduce: wrong (every further collective re-multiplied what was already summed) and, at 4096 environments per
 // GPU, 3-5x the cost of the step it followed.  Here:
 //   * the step kernels keep adding into the rank's accumulators `acc`;
-//   * dm_stats_allreduce launches this one-CTA kernel on the step's stream: it SNAPSHOTS-AND-ZEROES `acc`, writes the
-//     snapshot into slot [parity][rank] of EVERY rank's communication buffer (plain stores to peer-mapped memory, i.e.
-//     NVLink writes), fences, raises flag [parity][rank] = sequence number on every rank, waits until all of its own flags
-//     show the sequence number, and adds the slots -- summed in rank order, so every rank gets the same bits -- to the
+//   * an exchange SNAPSHOTS-AND-ZEROES `acc` (atomicExch per entry: a step kernel running beside it adds with atomicAdd,
+//     so every contribution lands either in this snapshot or in the next one and none is lost), writes the snapshot into
+//     line set [parity][rank] of EVERY rank's communication buffer (plain stores to peer-mapped memory, i.e. NVLink
+//     writes), and adds the lines of every rank -- summed in rank order, so every rank gets the same bits -- to the
 //     running global `total`.  Only snapshots are ever exchanged; `total` is never re-reduced.
+//   * Every value travels with its sequence number: one 16-byte line {low word, tag, high word, tag} per double, each
+//     8-byte half atomic on its own (the scheme of NCCL's LL protocol).  A sender needs no release fence and no separate
+//     flag -- the remote stores are fire-and-forget -- and the receiver validates each value by its two tags.
 //   * No host involvement, no NCCL launch, graph-capturable (the sequence number lives in device memory).
-//   * Auto mode (dm_stats_set_auto): the exchange rides INSIDE the step kernel as one extra CTA (peer_fused_cta): at the
-//     start of step k + 1's kernel it collects the exchange posted a step earlier and posts the sums of the steps up to k;
-//     no extra launch, no event, no exposed NVLink latency.  Measured alternatives (profiles/r02_collective.md): a
-//     separate exchange kernel between the steps 19.6 us/step at 2 x 4096 environments, the same kernel on a side stream
-//     behind an event 11.8 us (the event record costs the programmatic-launch overlap), ncclAllReduce of the snapshot 37 us.
-// Two slot sets (parity of the sequence number) make the exchange safe without a second barrier: a rank can start call
-// k + 1 (writing set (k+1) & 1) while a slower rank still reads set k & 1, and nobody can start call k + 2 before every
-// rank has raised its flag of call k + 1, i.e. has finished reading set k & 1.
+//   * dm_stats_allreduce launches the COMPLETE exchange (send, then wait for everyone's lines of the same number).
+//   * Auto mode (dm_stats_set_auto) uses the LAGGED exchange: take in the lines posted one exchange ago -- they have had
+//     a whole step to arrive -- and post the sums accumulated since; nothing waits for the exchange it posts.  The
+//     totals trail by one exchange while the loop runs; one dm_stats_allreduce at the end makes them exact.  It runs
+//     either as its own one-CTA kernel on a side stream with NO dependency on the step's stream in either direction
+//     (small launches: free SMs exist, and a kernel that has written to peer memory completes ~1.2 us later, which the
+//     step's stream must not wait for), or as one extra CTA of the step kernel (launches that fill the GPU, where a
+//     second kernel would have to wait for a free SM and the extra CTA is free).
+//     Measured at 2 x 4096 environments, an exchange every step (profiles/r02_collective.md): N = 1 8.6 us/step;
+//     ncclAllReduce of the snapshot 37; complete exchange kernel between the steps 17-20; the same behind an event on a
+//     side stream 11.8; extra CTA with flags + release fences 10.0-10.2; extra CTA, tagged lines 9.9-10.0; a PULL form
+//     (publish locally, read the peers) 11.8; lagged kernel on the side stream, no events **9.1**.
+// Two line sets (parity of the sequence number) make the exchange safe without a barrier: a rank sends exchange seq + 1
+// into set (seq + 1) & 1 only after it has received exchange seq from everyone, and a peer sent its seq only after it
+// had received seq - 1, the previous tenant of that set.
 // A rank that does not see its peers within kPeerTimeoutNs gives up, sets the error word and adds only what arrived: a
 // missing rank must never hang the GPU.
 #pragma once
@@ -27,28 +37,27 @@
 namespace dm {
 
 constexpr int kPeerMaxWorld = 8;
-constexpr int kPeerStride = 256;  // doubles per slot (n_stats <= 6 + 2 * 125)
+constexpr int kPeerStride = 256;  // values per line set (n_stats <= 6 + 2 * 125)
 constexpr unsigned long long kPeerTimeoutNs = 2000000000ull;
 
 struct PeerComm {  // one per rank, in that rank's device memory, mapped by every peer (cudaIpc)
-  double slots[2][kPeerMaxWorld][kPeerStride];
-  unsigned long long flags[2][kPeerMaxWorld];
+  uint4 line[2][kPeerMaxWorld][kPeerStride];  // {lo, tag, hi, tag} per value; set [parity][r] is written by rank r
 };
 
 struct PeerState {  // device memory, one per handle
   unsigned long long seq;  // sequence number of the last exchange posted
-  unsigned int pending;    // 1: exchange `seq` has been posted but not yet collected (fused mode)
+  unsigned int pending;    // 1: exchange `seq` has been posted but not yet received (lagged form)
   unsigned int err;        // 1: a peer did not arrive in time
 };
 
 struct PeerParams {
-  double* acc;                 // the rank's running accumulators (zeroed by a post)
+  double* acc;                 // the rank's running accumulators (zeroed by a send)
   double* snap;                // the rank's last snapshot (kept for inspection / the NCCL fallback)
   double* total;               // global running sums
   PeerState* st;
   PeerComm* comm[kPeerMaxWorld];  // comm[r] = rank r's buffer as mapped in THIS process (comm[rank] = own)
   int rank, world, n;
-  int enable;                  // fused mode: this launch carries an exchange CTA
+  int enable;                  // step kernel: this launch carries an exchange CTA
 };
 
 __device__ __forceinline__ unsigned long long peer_now() {
@@ -56,127 +65,91 @@ __device__ __forceinline__ unsigned long long peer_now() {
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
 }
-__device__ __forceinline__ void peer_store_release(unsigned long long* p, unsigned long long v) {
-  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+__device__ __forceinline__ void ll_store(uint4* p, double v, uint32_t tag) {
+  const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"((uint32_t)b), "r"(tag), "r"((uint32_t)(b >> 32)), "r"(tag)
+               : "memory");
 }
-__device__ __forceinline__ unsigned long long peer_load_acquire(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+__device__ __forceinline__ uint4 ll_load(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
   return v;
 }
-
-__device__ __forceinline__ unsigned long long peer_load_relaxed(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-
-// The four phases of an exchange, each executed by the whole CTA.  Ordering: the flag of exchange `seq` is stored with
-// release semantics after a CTA barrier that follows every thread's slot stores (cumulativity through bar.sync), and a
-// reader polls the flag relaxed, fences once, and passes a CTA barrier before anyone reads the slots.
-//
-// (1) wait until every rank has posted exchange `seq`
-__device__ __forceinline__ void peer_wait(const PeerParams& p, unsigned long long seq, int* s_late) {
-  if (p.world > 1 && threadIdx.x < p.world) {
-    const unsigned long long t0 = peer_now();
-    const unsigned long long* f = &p.comm[p.rank]->flags[int(seq & 1)][threadIdx.x];
-    while (peer_load_relaxed(f) < seq) {
-      __nanosleep(64);
-      if (peer_now() - t0 > kPeerTimeoutNs) {
-        atomicExch(s_late, 1);
-        break;
-      }
-    }
-    __threadfence_system();
-  }
-  __syncthreads();
-}
-// (2) snapshot-and-zero the accumulators and send the snapshot towards every rank's slot of exchange `seq`.  The snapshot
-// is atomic per entry: a step kernel running beside this (fused mode) adds with atomicAdd, so every contribution lands
-// either in this snapshot or in the next one and none is lost.  One rank: the snapshot goes straight to the totals.
-__device__ __forceinline__ void peer_send(const PeerParams& p, unsigned long long seq) {
+// snapshot-and-zero, then the snapshot towards every rank (the own lines too: the receiver treats all ranks alike).
+// One rank: the snapshot goes straight to the totals.
+__device__ __forceinline__ void ll_send(const PeerParams& p, unsigned long long seq) {
   const int par = int(seq & 1);
+  const uint32_t tag = (uint32_t)seq;
   for (int j = threadIdx.x; j < p.n; j += blockDim.x) {
     const double v = __longlong_as_double((long long)atomicExch(reinterpret_cast<unsigned long long*>(p.acc + j), 0ull));
     p.snap[j] = v;
     if (p.world > 1) {
-      for (int r = 0; r < p.world; ++r) p.comm[r]->slots[par][p.rank][j] = v;
+      for (int r = 0; r < p.world; ++r) ll_store(&p.comm[r]->line[par][p.rank][j], v, tag);
     } else {
       p.total[j] += v;
     }
   }
 }
-// (3) add the slots of exchange `seq` (all present: peer_wait) to the global totals, in rank order: the same bits everywhere
-__device__ __forceinline__ void peer_sum(const PeerParams& p, unsigned long long seq, const int* s_late) {
+// wait for exchange `seq` value by value and add it, in rank order, to the totals
+__device__ __forceinline__ void ll_recv(const PeerParams& p, unsigned long long seq) {
   if (p.world <= 1) return;
   const int par = int(seq & 1);
+  const uint32_t tag = (uint32_t)seq;
+  bool late = false;
   for (int j = threadIdx.x; j < p.n; j += blockDim.x) {
+    uint4 v[kPeerMaxWorld];
+    const unsigned long long t0 = peer_now();
+    for (;;) {
+      bool ok = true;
+#pragma unroll
+      for (int r = 0; r < kPeerMaxWorld; ++r)
+        if (r < p.world) {
+          v[r] = ll_load(&p.comm[p.rank]->line[par][r][j]);
+          ok = ok && v[r].y == tag && v[r].w == tag;
+        }
+      if (ok) break;
+      if (peer_now() - t0 > kPeerTimeoutNs) {
+        late = true;
+        break;
+      }
+      __nanosleep(64);
+    }
     double s = 0.0;
-    for (int r = 0; r < p.world; ++r) s += __ldcv(&p.comm[p.rank]->slots[par][r][j]);  // L1 may hold the lines of exchange seq - 2
+#pragma unroll
+    for (int r = 0; r < kPeerMaxWorld; ++r)
+      if (r < p.world && v[r].y == tag && v[r].w == tag)
+        s += __longlong_as_double((long long)(((unsigned long long)v[r].z << 32) | v[r].x));
     p.total[j] += s;
   }
-  if (threadIdx.x == 0 && *s_late) p.st->err = 1u;
-}
-// (4) tell every rank that this rank's slot of exchange `seq` is complete
-__device__ __forceinline__ void peer_raise(const PeerParams& p, unsigned long long seq) {
-  __syncthreads();
-  if (p.world > 1 && threadIdx.x < p.world) peer_store_release(&p.comm[threadIdx.x]->flags[int(seq & 1)][p.rank], seq);
+  if (late) p.st->err = 1u;
+  __syncthreads();  // every line of exchange `seq` has been read before this rank sends again
 }
 
-// The exchange CTA of the FUSED mode (one extra CTA of the step kernel, after griddepcontrol.wait: the previous step is
-// complete): take in the exchange posted one step ago -- its data has had a whole step to arrive, so the wait is a
-// formality -- and post the sums accumulated since.  The summation of the old exchange runs while the stores of the new
-// one cross NVLink, and nothing here waits for the exchange it posts: its latency lies behind the step's own compute.
-// The totals therefore trail by one exchange; dm_stats_allreduce (the explicit kernel below) takes in what is pending
-// and exchanges the remainder, which makes them exact.
-// Slot-set safety: set (seq+1) & 1 was last used by exchange seq - 1.  A peer raised its flag of exchange `seq` only
-// after it had summed seq - 1 (program order here), so having waited for `seq` this rank may overwrite that set.
-__device__ __forceinline__ void peer_fused_cta(const PeerParams& p) {
+// One exchange by one CTA.  complete = false: the LAGGED form (receive what was posted one exchange ago, post the sums
+// accumulated since); complete = true: additionally wait for the exchange just posted, which makes the totals exact.
+__device__ __forceinline__ void peer_exchange(const PeerParams& p, bool complete) {
   __shared__ unsigned long long s_seq;
   __shared__ unsigned int s_pending;
-  __shared__ int s_late;
   if (threadIdx.x == 0) {
     s_seq = p.st->seq;
     s_pending = p.st->pending;
-    s_late = 0;
   }
   __syncthreads();
   const unsigned long long seq = s_seq;
-  const bool pending = s_pending != 0;
-  if (pending) peer_wait(p, seq, &s_late);
-  peer_send(p, seq + 1);
-  if (pending) peer_sum(p, seq, &s_late);
-  peer_raise(p, seq + 1);
+  if (s_pending) ll_recv(p, seq);
+  ll_send(p, seq + 1);
+  if (complete) ll_recv(p, seq + 1);
   if (threadIdx.x == 0) {
     p.st->seq = seq + 1;
-    p.st->pending = p.world > 1 ? 1u : 0u;
+    p.st->pending = (!complete && p.world > 1) ? 1u : 0u;
   }
 }
-
-// The explicit exchange (dm_stats_allreduce): collect what the fused mode left pending, then a complete exchange.
-static __global__ void __launch_bounds__(kPeerStride) stats_exchange_kernel(const PeerParams p) {
-  __shared__ unsigned long long s_seq;
-  __shared__ unsigned int s_pending;
-  __shared__ int s_late;
-  if (threadIdx.x == 0) {
-    s_seq = p.st->seq;
-    s_pending = p.st->pending;
-    s_late = 0;
-  }
-  __syncthreads();
-  const unsigned long long seq = s_seq;
-  const bool pending = s_pending != 0;
-  if (pending) peer_wait(p, seq, &s_late);
-  peer_send(p, seq + 1);
-  if (pending) peer_sum(p, seq, &s_late);
-  peer_raise(p, seq + 1);
-  peer_wait(p, seq + 1, &s_late);
-  peer_sum(p, seq + 1, &s_late);
-  if (threadIdx.x == 0) {
-    p.st->seq = seq + 1;
-    p.st->pending = 0u;
-  }
-}
+// the exchange CTA of the step kernel (dm_tile_kernel.cuh)
+__device__ __forceinline__ void peer_fused_cta(const PeerParams& p) { peer_exchange(p, false); }
+// the lagged exchange as its own kernel, for the side stream of the auto mode
+static __global__ void __launch_bounds__(kPeerStride) stats_exchange_lagged_kernel(const PeerParams p) { peer_exchange(p, false); }
+// the explicit exchange (dm_stats_allreduce): receive what the auto mode left pending, then a complete exchange
+static __global__ void __launch_bounds__(kPeerStride) stats_exchange_kernel(const PeerParams p) { peer_exchange(p, true); }
 
 // pieces of the checked fallback (NCCL all-reduce of the SNAPSHOT between them): acc -> snap (zeroing acc); total += snap
 static __global__ void stats_snapshot_kernel(double* acc, double* snap, int n) {

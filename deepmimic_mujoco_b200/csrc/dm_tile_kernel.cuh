@@ -160,6 +160,7 @@ struct TileExtra {
   int table_floats;  // packed clip table size (floats); staged in shared memory when TABLE_SMEM
   int nbuf;          // ring slots (>= groups per CTA); nbuf - groups tiles are always loading ahead of the groups
   int skip_compute;  // experiment: memory skeleton only (no env_step)
+  int n_cta;         // CTAs that walk tiles: blockIdx.x < n_cta; CTA n_cta is the exchange CTA (if any)
   PeerParams peer;   // peer.enable: the launch has one CTA more than tiles need, the statistics exchange CTA (dm_peer.cuh)
 };
 
@@ -197,7 +198,7 @@ __global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_co
   uint64_t* rbar = bars + TC::MAXBUF + 1 + (group < 3 ? group : 2);
   // this CTA's tiles are blockIdx.x + j * ncta, j = 0 .. nt-1; tile j sits in ring slot j % nbuf and is
   // processed by group j % n_groups
-  const int ncta = (int)gridDim.x - (STATS && x.peer.enable ? 1 : 0);  // CTAs that walk tiles
+  const int ncta = x.n_cta;  // CTAs that walk tiles
   const int nt = (int)blockIdx.x < x.n_tiles ? (x.n_tiles - 1 - (int)blockIdx.x) / ncta + 1 : 0;
   auto issue_load = [&](int j) {  // one thread
     const int slot = j % nbuf;

@@ -57,6 +57,7 @@ struct dm_handle {
   long long auto_count = 0;
   struct SoaMapEntry { const void *q, *v, *o; long long ld; int n; SoaMaps maps; };
   std::vector<SoaMapEntry> soa_maps;  // tensor maps of the SoA buffer sets seen lately (encoding costs a few us per call)
+  int exch_where = 0;                        // where the auto mode's last exchange went: 0 nowhere / ordered, 1 the step's stream, 2 the side stream
   bool fuse_now = false, fused_done = false;  // this dm_step is due an exchange / the tile kernel carried it (exchange CTA)
   cudaStream_t coll_stream = nullptr;       // side stream of the auto mode
   cudaEvent_t coll_event = nullptr;
@@ -645,7 +646,7 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
       const bool row_stage = wide && !table_smem && !h->skip_compute && h->row_stage_override != 0 && G <= 3 &&
                              smem + row_stage_bytes <= TC::SMEM_BUDGET;
       if (row_stage) smem += row_stage_bytes;
-      TileExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float)), nbuf, h->skip_compute};
+      TileExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float)), nbuf, h->skip_compute, grid};
       const bool fused = h->fuse_now && a->accumulate_stats;  // one more CTA: the statistics exchange (dm_peer.cuh)
       if (fused) {
         static const int dbg = getenv("DM_PEER_DEBUG") ? atoi(getenv("DM_PEER_DEBUG")) : 1;
@@ -701,19 +702,37 @@ extern "C" int dm_step(dm_handle* h, const dm_step_args* a) {
   int rc = check_step_args(h, a, "dm_step");
   if (rc) return rc;
   CU(h, cudaSetDevice(h->device));
-  // auto mode of the collective: every auto_every-th step with statistics carries an exchange -- as one extra CTA of the
-  // tile kernel where that kernel runs (the normal case), else as its own kernel on the side stream behind the step
+  // auto mode of the collective: every auto_every-th step with statistics comes with a lagged exchange (dm_peer.cuh).
+  // Launches that leave SMs free (at most one tile per SM) get it as a one-CTA kernel on the side stream, with no
+  // dependency on this stream in either direction: a kernel that has written peer memory completes ~1.2 us late, and
+  // the next step must not wait for that (2 x 4096 envs: 9.1 us per step against 9.9 with the exchange CTA, 8.6 alone).
+  // Launches that fill the GPU carry it as one extra CTA of the tile kernel, where it is free (1 M envs: 169.2 vs 169.5 us)
+  // and a second kernel would wait for an SM.  DM_PEER_SIDE = 0 / 1 forces one or the other.
   const bool due = h->auto_every > 0 && a->accumulate_stats && a->n > 0 && (h->auto_count + 1) % h->auto_every == 0;
-  h->fuse_now = due;
+  const char* side_env = due ? getenv("DM_PEER_SIDE") : nullptr;  // read per exchange: the tests switch routes between steps
+  const bool side = side_env ? atoi(side_env) != 0 : (a->n + 127) / 128 <= h->num_sms;
+  h->fuse_now = due && !side;
   h->fused_done = false;
+  if (h->fuse_now && h->exch_where == 2) {  // exchanges share the sequence number: this one goes behind those on the side stream
+    CU(h, cudaEventRecord(h->coll_event, h->coll_stream));
+    CU(h, cudaStreamWaitEvent((cudaStream_t)a->stream, h->coll_event, 0));
+  }
   rc = launch_step(h, a, (cudaStream_t)a->stream);
   h->fuse_now = false;
   if (rc) return rc;
   if (h->auto_every > 0 && a->accumulate_stats && a->n > 0) ++h->auto_count;
+  if (due && h->fused_done) h->exch_where = 1;
   if (!due || h->fused_done) return DM_OK;
-  CU(h, cudaEventRecord(h->coll_event, (cudaStream_t)a->stream));
-  CU(h, cudaStreamWaitEvent(h->coll_stream, h->coll_event, 0));
-  return issue_exchange(h, h->coll_stream);
+  // (also the launch shapes without an exchange CTA: SoA, tails, the team kernel)
+  if (h->exch_where == 1) {  // ... and this one behind the exchange CTA of an earlier step
+    CU(h, cudaEventRecord(h->coll_event, (cudaStream_t)a->stream));
+    CU(h, cudaStreamWaitEvent(h->coll_stream, h->coll_event, 0));
+  }
+  h->exch_where = 2;
+  stats_exchange_lagged_kernel<<<1, kPeerStride, 0, h->coll_stream>>>(peer_params(h, 1));
+  CU(h, cudaGetLastError());
+  h->launches++;
+  return DM_OK;
 }
 
 static int launch_reset(dm_handle* h, const dm_reset_args* a, cudaStream_t s) {
@@ -1572,7 +1591,13 @@ extern "C" int dm_stats_allreduce(dm_handle* h, void* stream) {
     CU(h, cudaEventRecord(h->coll_event, h->coll_stream));
     CU(h, cudaStreamWaitEvent((cudaStream_t)stream, h->coll_event, 0));
   }
-  return issue_exchange(h, (cudaStream_t)stream);
+  rc = issue_exchange(h, (cudaStream_t)stream);
+  if (rc == DM_OK && h->coll_stream) {  // ... and those the auto mode issues next go behind this one (they share the sequence number)
+    CU(h, cudaEventRecord(h->coll_event, (cudaStream_t)stream));
+    CU(h, cudaStreamWaitEvent(h->coll_stream, h->coll_event, 0));
+    h->exch_where = 0;
+  }
+  return rc;
 }
 
 static PeerParams peer_params(const dm_handle* h, int enable) {

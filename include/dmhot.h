@@ -210,7 +210,8 @@ int dm_stats_read(dm_handle* h, double* host_out, void* stream);
  * rank and adds the sum (taken in rank order: the same bits on every rank) to the handle's GLOBAL TOTALS, which
  * dm_stats_read_total returns and dm_policy_normalizer_from_stats uses from then on.  Only snapshots are ever reduced,
  * never running sums.  The exchange is ONE single-CTA kernel on `stream` that writes into the other GPUs' memory over
- * NVLink (cudaIpc peer mappings) and waits on flags there: no host round trip, no NCCL launch, capturable in a CUDA graph.
+ * NVLink (cudaIpc peer mappings; every value travels with its sequence number, so there are no flags and no fences) and
+ * waits for the peers' values there: no host round trip, no NCCL launch, capturable in a CUDA graph.
  * Every rank must call it the same number of times; a rank that waits longer than 2 s for a peer gives up and
  * dm_stats_read_total then fails with DM_E_STATE.  With one rank (no dm_stats_peer_import) it is the local
  * snapshot -> totals move.  dm_stats_zero also clears the snapshot and the totals.
@@ -225,15 +226,15 @@ int dm_stats_allreduce(dm_handle* h, void* stream);
 int dm_stats_snapshot(dm_handle* h, double** snapshot_dev_ptr, void* stream);
 int dm_stats_commit(dm_handle* h, void* stream);
 int dm_stats_read_total(dm_handle* h, double* host_out, void* stream);
-/* Auto mode: every `every`-th dm_step with accumulate_stats = 1 carries an exchange itself (0 = off).  Where the tile
- * kernel runs (row-major batches of >= 128 environments, the normal case) the exchange is ONE EXTRA CTA of that kernel:
- * once the previous step is complete it collects the exchange posted one step earlier -- whose data has had a whole
- * step to cross NVLink -- and posts the sums accumulated since; no extra launch, no event, no exposed latency.  The
- * global totals therefore trail the steps by up to two exchanges while the loop runs; one dm_stats_allreduce after the
- * last step collects what is pending and exchanges the remainder, after which dm_stats_read_total is exact.  Snapshots
- * are taken atomically, so no contribution is ever lost or counted twice.  Other launch shapes fall back to the
- * exchange kernel on a side stream owned by the handle, ordered behind the step by an event.
- * dm_stats_join makes `stream` wait for every exchange issued on that side stream so far. */
+/* Auto mode: every `every`-th dm_step with accumulate_stats = 1 comes with a LAGGED exchange (0 = off): it takes in what
+ * every rank posted one exchange earlier -- those values have had a whole step to cross NVLink -- and posts the sums
+ * accumulated since; nothing waits for the exchange it posts.  Steps of at most one tile per SM (<= 128 x SM-count
+ * environments) get it as a one-CTA kernel on a side stream owned by the handle, with no dependency on the step's
+ * stream in either direction; larger steps carry it as ONE EXTRA CTA of the step kernel (no extra launch).  The global
+ * totals therefore trail the steps by up to two exchanges while the loop runs; one dm_stats_allreduce after the last
+ * step takes in what is pending and exchanges the remainder, after which dm_stats_read_total is exact.  Snapshots are
+ * taken atomically per value, so no contribution is ever lost or counted twice.
+ * dm_stats_join makes `stream` wait for every exchange issued on the side stream so far (dm_stats_allreduce does so itself). */
 int dm_stats_set_auto(dm_handle* h, int32_t every);
 int dm_stats_join(dm_handle* h, void* stream);
 

@@ -4,9 +4,11 @@ collective after the steps -- against ONE GPU stepping the whole batch:
   * sharded observations / rewards / flags / counters == single-GPU outputs bit for bit;
   * the collective's global totals == float64 numpy over the concatenated batches (count exact), the same bits on both
     ranks, over several step -> reduce cycles on a running accumulator (one or two steps between reductions);
-  * three routes: the device-side peer exchange launched between the steps (dm_stats_allreduce), the same exchange riding
-    inside the step kernel as its extra CTA (dm_stats_set_auto, one explicit exchange at the end), and the NCCL fallback
-    on the snapshot."""
+  * five routes: the device-side peer exchange launched between the steps (dm_stats_allreduce); the auto mode
+    (dm_stats_set_auto, one explicit exchange at the end) with the lagged exchange as its own kernel on the side stream
+    ("auto": what 768 environments per rank get), as the extra CTA of the step kernel ("fused"), and switching between the
+    two from step to step ("mixed": the exchanges share one sequence number across two streams); the NCCL fallback on the
+    snapshot."""
 import os
 import socket
 
@@ -34,7 +36,7 @@ def _states(hp, n, batches):
     return bench.synth_states(hp, n, batches, 31, torch.device("cpu"))
 
 
-def _step_all(hp, s, dev, lo, hi, batches, reduce=None):
+def _step_all(hp, s, dev, lo, hi, batches, reduce=None, before_step=None):
     import torch
     d = hp.dims
     n = hi - lo
@@ -42,6 +44,8 @@ def _step_all(hp, s, dev, lo, hi, batches, reduce=None):
     b = 0
     for k in CYCLES:
         for _ in range(k):
+            if before_step is not None:
+                before_step(b)
             t = {key: v[b, lo:hi].contiguous().to(dev) for key, v in s.items()}
             out = dict(obs=torch.zeros(n, d.obs_dim, device=dev), reward=torch.zeros(n, device=dev),
                        done=torch.zeros(n, dtype=torch.uint8, device=dev), ep_return=torch.zeros(n, device=dev))
@@ -73,11 +77,14 @@ def _worker(rank, world, port, q, route):
     with torch.cuda.device(dev):
         coll = dmdist.StatsCollective(hp, force_nccl=force_nccl)
         hp.stats_zero()
-        if route == "auto":  # every step carries an exchange; one explicit exchange afterwards makes the totals exact
+        if route in ("auto", "fused", "mixed"):  # every step comes with an exchange; one explicit exchange afterwards makes the totals exact
             assert coll.auto(1)
-            res = _step_all(hp, s, dev, lo, hi, batches, lambda: None)
+            pick = {"auto": lambda b: None, "fused": lambda b: os.environ.update(DM_PEER_SIDE="0"),
+                    "mixed": lambda b: os.environ.update(DM_PEER_SIDE=str(b % 2))}[route]
+            res = _step_all(hp, s, dev, lo, hi, batches, lambda: None, pick)
             coll.reduce()
             coll.auto(0)
+            os.environ.pop("DM_PEER_SIDE", None)
         else:
             res = _step_all(hp, s, dev, lo, hi, batches, coll.reduce)
         torch.cuda.synchronize()
@@ -96,7 +103,7 @@ def _worker(rank, world, port, q, route):
 
 
 @pytest.mark.timeout(300)
-@pytest.mark.parametrize("route", ["peer", "auto", "nccl"])
+@pytest.mark.parametrize("route", ["peer", "auto", "fused", "mixed", "nccl"])
 def test_two_ranks_equal_one_gpu(route):
     force_nccl = route == "nccl"
     import torch

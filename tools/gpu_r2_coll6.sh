@@ -1,0 +1,29 @@
+# push vs pull form of the statistics exchange, and the effect of a pre-filled launch queue (2 GPUs)
+set -u
+mkdir -p gpurun_out
+N=${NG:-2}
+one() { python - "$1" "$2" <<'PY'
+import json,sys
+try:
+    d=json.loads(open(sys.argv[2]).read().strip().splitlines()[-1])
+    c=d.get('stats',{}).get('count')
+    print('%-44s %8.2f us/step  total %7.1f us  count %s/%s' % (sys.argv[1], d['ms_per_step']*1e3, d['ms_per_step']*1e3*d['steps'], c, d['n_gpus']*4096*d['steps']))
+except Exception as e:
+    print(sys.argv[1], 'ERR', e)
+PY
+}
+R1="python bench.py --gpus 1 --no-cpu --no-e2e --no-sweep --no-configs --warmup 5"
+R="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N --no-cpu --no-e2e --no-sweep --no-configs --warmup 5"
+# multirank parity with the pull form first
+DM_PEER_PULL=1 timeout 600 python -m pytest tests/test_gpu_multirank.py -x -q 2>&1 | tail -3
+for rep in 1 2; do
+for st in 20 200; do
+timeout 300 $R1 --steps $st > gpurun_out/g.json 2>/dev/null; one "N=1 steps=$st" gpurun_out/g.json
+DM_BENCH_GATE_US=300 timeout 300 $R1 --steps $st > gpurun_out/g.json 2>/dev/null; one "N=1 steps=$st gate" gpurun_out/g.json
+timeout 300 $R --steps $st > gpurun_out/g.json 2>/dev/null; one "N=$N steps=$st push" gpurun_out/g.json
+DM_PEER_PULL=1 timeout 300 $R --steps $st > gpurun_out/g.json 2>/dev/null; one "N=$N steps=$st pull" gpurun_out/g.json
+DM_BENCH_GATE_US=300 timeout 300 $R --steps $st > gpurun_out/g.json 2>/dev/null; one "N=$N steps=$st push gate" gpurun_out/g.json
+DM_BENCH_GATE_US=300 DM_PEER_PULL=1 timeout 300 $R --steps $st > gpurun_out/g.json 2>/dev/null; one "N=$N steps=$st pull gate" gpurun_out/g.json
+DM_BENCH_GATE_US=300 timeout 300 $R --steps $st --collective off > gpurun_out/g.json 2>/dev/null; one "N=$N steps=$st off gate" gpurun_out/g.json
+done
+done
