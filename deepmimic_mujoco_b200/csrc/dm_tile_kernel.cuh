@@ -161,6 +161,7 @@ struct TileExtra {
   int nbuf;          // ring slots (>= groups per CTA); nbuf - groups tiles are always loading ahead of the groups
   int skip_compute;  // experiment: memory skeleton only (no env_step)
   int n_cta;         // CTAs that walk tiles: blockIdx.x < n_cta; CTA n_cta is the exchange CTA (if any)
+  int no_prefetch;   // experiment (DM_NO_PREFETCH): no L2 prefetch of the first tile in front of griddepcontrol.wait
   PeerParams peer;   // peer.enable: the launch has one CTA more than tiles need, the statistics exchange CTA (dm_peer.cuh)
 };
 
@@ -253,6 +254,14 @@ __global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_co
     s_motor[2 * TC::NUP + k] = hi;
   }
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  // While the previous kernel of the stream finishes: pull the group's first tile towards L2.  A prefetch is a hint and L2
+  // is the point of coherence, so this is safe even when that kernel is still writing these very rows.
+  if (gt == 0 && group < nt && !x.no_prefetch) {
+    const long long f0 = ((long long)blockIdx.x + (long long)group * ncta) * TE;
+    l2_prefetch(p.qpos + f0 * Rb::NQ, sizeof(float) * TE * Rb::NQ);
+    l2_prefetch(p.qvel + f0 * Rb::NV, sizeof(float) * TE * Rb::NV);
+    if (p.torque) l2_prefetch(p.action + f0 * Rb::NA, sizeof(float) * TE * Rb::NA);
+  }
   asm volatile("griddepcontrol.wait;" ::: "memory");
   if (gt == 0) {  // fill the ring: every leader its own first tile, leader 0 the slots beyond the groups
     if (group < nt) issue_load(group);

@@ -646,7 +646,9 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
       const bool row_stage = wide && !table_smem && !h->skip_compute && h->row_stage_override != 0 && G <= 3 &&
                              smem + row_stage_bytes <= TC::SMEM_BUDGET;
       if (row_stage) smem += row_stage_bytes;
-      TileExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float)), nbuf, h->skip_compute, grid};
+      TileExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float)), nbuf, h->skip_compute, grid, 0};
+      static const int no_prefetch = getenv("DM_NO_PREFETCH") ? atoi(getenv("DM_NO_PREFETCH")) : 0;
+      ex.no_prefetch = no_prefetch;
       const bool fused = h->fuse_now && a->accumulate_stats;  // one more CTA: the statistics exchange (dm_peer.cuh)
       if (fused) {
         static const int dbg = getenv("DM_PEER_DEBUG") ? atoi(getenv("DM_PEER_DEBUG")) : 1;
