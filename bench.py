@@ -215,7 +215,7 @@ class Workload:
             for k in ("qpos", "qvel", "action"):
                 s[k] = s[k].transpose(1, 2).contiguous()  # [B, dim, N]
         self.s = s
-        self.idx0, self.ep0 = s["idx"].clone(), s["ep_len"].clone()
+        self.idx0, self.ep0, self.clip0 = s["idx"].clone(), s["ep_len"].clone(), s["clip"].clone()
         shape = (lambda dim: (self.B, dim, n_envs)) if self.soa else (lambda dim: (self.B, n_envs, dim))
         self.obs = torch.zeros(shape(d.obs_dim), device=device)
         self.torque = torch.zeros(shape(d.nu), device=device)
@@ -230,6 +230,7 @@ class Workload:
     def restore(self):
         self.s["idx"].copy_(self.idx0)
         self.s["ep_len"].copy_(self.ep0)
+        self.s["clip"].copy_(self.clip0)  # the combined env's motion state is in-out too: every region starts from the seeded batch
 
     def step(self):
         b = self.i % self.B

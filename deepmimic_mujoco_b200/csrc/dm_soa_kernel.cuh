@@ -48,6 +48,7 @@ struct SoaExtra {
   int n_tiles;       // full tiles in this launch
   int table_floats;  // packed clip table size (floats); staged in shared memory when TABLE_SMEM
   int table_pad;     // ... rounded up to a multiple of 32 floats: tensor-map copies want 128-byte aligned shared memory
+  int prefetch;      // L2 prefetch of the group's next tile (DM_PREFETCH_NEXT=0 switches it off)
 };
 
 // tensor maps of one launch (encoded on the host, dmhot.cu): qpos [nq, ld] box {128, nq}; qvel box {128, nv};
@@ -56,6 +57,9 @@ struct alignas(64) SoaMaps {
   CUtensorMap q, v, oj, oc;
 };
 
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* tm, int c0, int c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];" ::"l"(tm), "r"(c0), "r"(c1) : "memory");
+}
 __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* tm, int c0, int c1, uint64_t* bar) {
   asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
                    smem_u32(dst)),
@@ -116,6 +120,11 @@ __global__ void __launch_bounds__(128 * G, 1) step_soa_kernel(const __grid_const
   const int t_base = blockIdx.x * n_groups + group, t_stride = gridDim.x * n_groups;
   const int nt = t_base < x.n_tiles ? (x.n_tiles - 1 - t_base) / t_stride + 1 : 0;
   uint64_t* bar = bars + group;
+  auto prefetch = [&](int j) {  // one thread: tile j's boxes towards L2 (a hint; safe before griddepcontrol.wait)
+    const int e0 = (t_base + j * t_stride) * TE;
+    tma_prefetch_2d(&tm.q, e0, 0);
+    tma_prefetch_2d(&tm.v, e0, 0);
+  };
   auto issue_load = [&](int j) {  // one thread: the qpos box and the qvel box of tile j
     const int e0 = (t_base + j * t_stride) * TE;
     mbar_expect_tx(bar, sizeof(float) * TE * (NQ + NV));
@@ -137,6 +146,7 @@ __global__ void __launch_bounds__(128 * G, 1) step_soa_kernel(const __grid_const
   }
   const float* rows_tab = TABLE_SMEM ? s_table : p.cs.rows;
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (gt == 0 && nt > 0 && x.prefetch) prefetch(0);
   asm volatile("griddepcontrol.wait;" ::: "memory");
   if (gt == 0 && nt > 0) issue_load(0);
   bool table_ready = !TABLE_SMEM;
@@ -153,6 +163,8 @@ __global__ void __launch_bounds__(128 * G, 1) step_soa_kernel(const __grid_const
     // action -> torque while the tile's bulk copies are in flight: for a fixed actuator the group's threads read and
     // write 512 consecutive bytes of the action / torque rows (the actions are not staged: 14 KB per slot that the clip
     // table needs -- with them in the slot the table fell out of shared memory and every step gathered its row from L2)
+    // (ncu has 14 % of the G1 kernel's stall samples on the first use of these loads; loading them one tile ahead into
+    // registers moved the stall elsewhere -- G1 combined, 1 M envs 272 -> 276 us -- and spilled in the four-group kernels)
     if (want_tau) {
       float av[NA];
 #pragma unroll
@@ -173,6 +185,10 @@ __global__ void __launch_bounds__(128 * G, 1) step_soa_kernel(const __grid_const
       table_ready = true;
     }
     mbar_wait(bar, j & 1);
+    // the next tile crosses HBM -> L2 while this one is computed (262144 humanoid3d envs 59.5 -> 52.6 us; nothing at 1 M envs).
+    // Prefetching the NA action rows of the next tile the same way (512 bytes each) was measured far slower: G1 combined,
+    // 1 M envs 272 -> 334 us.
+    if (gt == 0 && j + 1 < nt && x.prefetch) prefetch(j + 1);
     SoaIO<KIND, Rb> io{s_q + gt, s_v + gt, s_c + gt};
     StepOut so;
     env_step<KIND, Rb, SoaIO<KIND, Rb>, TERMS>(io, p.cs, rows_tab, st, contact, so);

@@ -571,7 +571,8 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
       const int grid = (n_tiles + G - 1) / G < h->num_sms ? (n_tiles + G - 1) / G : h->num_sms;
       StepParams q = p;
       q.n = tiled;
-      SoaExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float)), (int)(table_pad / sizeof(float))};
+      SoaExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float)), (int)(table_pad / sizeof(float)),
+                  getenv("DM_PREFETCH_NEXT") ? atoi(getenv("DM_PREFETCH_NEXT")) : 1};
       const SoaMaps* maps = nullptr;
       for (const auto& m : h->soa_maps)
         if (m.q == a->qpos && m.v == a->qvel && m.o == a->obs && m.ld == a->ld && m.n == tiled) { maps = &m.maps; break; }
@@ -646,7 +647,9 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
       const bool row_stage = wide && !table_smem && !h->skip_compute && h->row_stage_override != 0 && G <= 3 &&
                              smem + row_stage_bytes <= TC::SMEM_BUDGET;
       if (row_stage) smem += row_stage_bytes;
-      TileExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float)), nbuf, h->skip_compute, grid, 0};
+      TileExtra ex{a->accumulate_stats ? h->d_stats : nullptr, n_tiles, (int)(table_bytes / sizeof(float)), nbuf, h->skip_compute, grid, 0, 0};
+      static const int prefetch_next = getenv("DM_PREFETCH_NEXT") ? atoi(getenv("DM_PREFETCH_NEXT")) : 1;
+      ex.prefetch_next = prefetch_next;
       static const int no_prefetch = getenv("DM_NO_PREFETCH") ? atoi(getenv("DM_NO_PREFETCH")) : 0;
       ex.no_prefetch = no_prefetch;
       const bool fused = h->fuse_now && a->accumulate_stats;  // one more CTA: the statistics exchange (dm_peer.cuh)

@@ -1,0 +1,20 @@
+set -u
+mkdir -p gpurun_out
+one() { python - "$1" "$2" <<'PY'
+import json,sys
+try:
+    d=json.loads(open(sys.argv[2]).read().strip().splitlines()[-1])
+    print('%-44s %8.2f us/step kernel %.2f us frac %.3f' % (sys.argv[1], d['ms_per_step']*1e3, d['roofline']['kernel_ms']*1e3, d['roofline']['frac']))
+except Exception as e:
+    print(sys.argv[1], 'ERR', e)
+PY
+}
+R1="python bench.py --gpus 1 --no-cpu --no-e2e --no-sweep --no-configs --warmup 5 --steps 20"
+for rep in 1 2; do
+timeout 300 $R1 --envs 1048576 --layout soa --robot unitree_g1 --combined > gpurun_out/g.json 2>gpurun_out/g.err; one "g1c soa 1M" gpurun_out/g.json
+timeout 300 $R1 --envs 262144 --layout soa --robot unitree_g1 --combined > gpurun_out/g.json 2>gpurun_out/g.err; one "g1c soa 262144" gpurun_out/g.json
+timeout 300 $R1 --envs 65536 --layout soa --robot unitree_g1 --combined > gpurun_out/g.json 2>gpurun_out/g.err; one "g1c soa 65536" gpurun_out/g.json
+timeout 300 $R1 --envs 1048576 --layout soa --robot unitree_g1 > gpurun_out/g.json 2>gpurun_out/g.err; one "g1 DPEnv soa 1M" gpurun_out/g.json
+timeout 300 $R1 --envs 1048576 --layout soa > gpurun_out/g.json 2>gpurun_out/g.err; one "h soa 1M" gpurun_out/g.json
+done
+timeout 1500 python -m pytest tests -x -q -m gpu 2>&1 | tail -4
