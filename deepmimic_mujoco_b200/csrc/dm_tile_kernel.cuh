@@ -141,7 +141,9 @@ template <class Rb>
 struct KernelGroups {  // measured on humanoid3d: G = 5 (96 registers, ~330 B of spills) is 40 % slower than G = 4
   static constexpr int G = 4 * 128 / DM_TE;
   // batches of at most WIDE_WANT tiles per SM run the instantiation compiled for GWIDE groups (no register cap)
-  static constexpr int GWIDE = 2, WIDE_WANT = 2;
+  // (with the L2 prefetch of round 2 the wide shape also wins at four tiles per SM: 65536 envs 17.9 -> 17.2 us walk,
+  // 18.7 -> 17.2 us spinkick + dance_b; at seven tiles per SM it loses, 30.8 vs 28.4 us)
+  static constexpr int GWIDE = 2, WIDE_WANT = 4;
   // in between, three groups at 164 registers (no spills) plus ONE lookahead ring slot beat four capped groups:
   // 262144 envs 52.2 vs 55.5 us, 524288 envs 91.0 vs 94.8, 1 M envs 168.1 vs 172.7; at 4 M envs 639 vs 634 (four groups again)
   static constexpr int GMID = 3, MID_WANT_LO = 8, MID_WANT_HI = 80, MID_NBUF = 4;

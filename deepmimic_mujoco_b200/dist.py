@@ -76,7 +76,8 @@ class StatsCollective:
     """The one collective of the path for a HotPath handle per rank.
 
     mode "peer"  : dm_stats_allreduce -- one single-CTA kernel per call that exchanges the snapshot through peer-mapped
-                   memory over NVLink (csrc/dm_peer.cuh); no host-enqueued collective in the step loop.
+                   memory over NVLink (csrc/dm_peer.cuh: tagged 16-byte lines, no flags, no fences); no host-enqueued
+                   collective in the step loop.  auto(every) lets dm_step issue a lagged exchange itself.
     mode "nccl"  : checked fallback when the cudaIpc mapping is not available: dm_stats_snapshot, ncclAllReduce of the
                    snapshot through torch.distributed, dm_stats_commit.
     mode "local" : world size 1.
@@ -124,8 +125,10 @@ class StatsCollective:
             self.hp.stats_allreduce()
 
     def auto(self, every):
-        """Let dm_step issue the exchange itself (side stream, overlapping the next step).  Only the device-side routes can
-        do that; returns False in "nccl" mode, where the caller keeps calling reduce()."""
+        """Let dm_step issue a LAGGED exchange itself with every `every`-th step (small steps: a one-CTA kernel on a
+        dependency-free side stream; steps that fill the GPU: one extra CTA of the step kernel).  The totals trail by one
+        exchange until the next reduce().  Only the device-side route can do that; returns False in "nccl" mode, where the
+        caller keeps calling reduce()."""
         if self.mode == "nccl":
             return False
         self.hp.stats_set_auto(every)

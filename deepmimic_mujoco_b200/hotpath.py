@@ -360,7 +360,7 @@ class HotPath:
         N.check(self.L.dm_stats_commit(self.h, stream), self.h, "dm_stats_commit")
 
     def stats_set_auto(self, every):
-        """every > 0: dm_step issues the exchange itself behind every `every`-th step with statistics, on a side stream."""
+        """every > 0: dm_step issues a lagged exchange itself with every `every`-th step with statistics (dm_stats_set_auto)."""
         N.check(self.L.dm_stats_set_auto(self.h, int(every)), self.h, "dm_stats_set_auto")
 
     def stats_join(self, stream=None):
