@@ -82,9 +82,77 @@ DM_HD void dm_sincos_f(float x, float& s, float& c) {
   c = dm_u2f(dm_f2u(cc) ^ (((k + 1u) << 30) & 0x80000000u));
 }
 DM_HD void dm_sincos_half(float theta, float& s, float& c) { dm_sincos_f(0.5f * theta, s, c); }
+
+// Two hinges at once.  On the device the fp32 version runs the argument reduction and both polynomials of BOTH angles in
+// Blackwell's packed fp32 arithmetic (fma / mul / add .rn.f32x2, SASS FFMA2 / FMUL2 / FADD2: one issue slot for two lanes,
+// constants as broadcast immediates), lane for lane the same IEEE operations as dm_sincos_f, so the results are bit-identical
+// to two scalar calls: 14 packed + 4 constant moves + 14 integer / select instructions for the pair against 2 x 25.  The
+// generated FK pairs consecutive hinges (tools/gen_model_code.py).
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ unsigned long long dm_pk2(float lo, float hi) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void dm_upk2(unsigned long long v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ unsigned long long dm_fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+  unsigned long long r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ unsigned long long dm_mul2(unsigned long long a, unsigned long long b) {
+  unsigned long long r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ unsigned long long dm_add2(unsigned long long a, unsigned long long b) {
+  unsigned long long r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ void dm_sincos_sign(uint32_t k, float ps, float pc, float& s, float& c) {
+  const bool swap = (k & 1u) != 0;
+  const float ss = swap ? pc : ps, cc = swap ? ps : pc;
+  s = dm_u2f(dm_f2u(ss) ^ ((k << 30) & 0x80000000u));
+  c = dm_u2f(dm_f2u(cc) ^ (((k + 1u) << 30) & 0x80000000u));
+}
+#endif
+DM_HD void dm_sincos_half2(float ta, float tb, float& sa, float& ca, float& sb, float& cb) {
+#if defined(__CUDA_ARCH__)
+#define DM_K2(v) dm_pk2(v, v)
+  const unsigned long long x = dm_mul2(dm_pk2(ta, tb), DM_K2(0.5f));
+  const unsigned long long t = dm_fma2(x, DM_K2(0.63661977236758134f), DM_K2(12582912.0f));
+  const unsigned long long kf = dm_add2(t, DM_K2(-12582912.0f));
+  unsigned long long r = dm_fma2(kf, DM_K2(-1.5707963705062866f), x);
+  r = dm_fma2(kf, DM_K2(4.371138828673793e-8f), r);
+  const unsigned long long r2 = dm_mul2(r, r);
+  unsigned long long ps = dm_fma2(r2, DM_K2(-1.9515295891e-4f), DM_K2(8.3321608736e-3f));
+  ps = dm_fma2(ps, r2, DM_K2(-1.6666654611e-1f));
+  ps = dm_fma2(dm_mul2(ps, r2), r, r);
+  unsigned long long pc = dm_fma2(r2, DM_K2(2.443315711809948e-5f), DM_K2(-1.388731625493765e-3f));
+  pc = dm_fma2(pc, r2, DM_K2(4.166664568298827e-2f));
+  pc = dm_fma2(dm_mul2(pc, r2), r2, dm_fma2(r2, DM_K2(-0.5f), DM_K2(1.0f)));
+#undef DM_K2
+  float t0, t1, ps0, ps1, pc0, pc1;
+  dm_upk2(t, t0, t1);
+  dm_upk2(ps, ps0, ps1);
+  dm_upk2(pc, pc0, pc1);
+  dm_sincos_sign(dm_f2u(t0), ps0, pc0, sa, ca);
+  dm_sincos_sign(dm_f2u(t1), ps1, pc1, sb, cb);
+#else
+  dm_sincos_half(ta, sa, ca);
+  dm_sincos_half(tb, sb, cb);
+#endif
+}
 DM_HD void dm_sincos_half(double theta, double& s, double& c) {
   s = sin(0.5 * theta);
   c = cos(0.5 * theta);
+}
+DM_HD void dm_sincos_half2(double ta, double tb, double& sa, double& ca, double& sb, double& cb) {
+  dm_sincos_half(ta, sa, ca);
+  dm_sincos_half(tb, sb, cb);
 }
 
 DM_HD float dm_rsqrt(float x) {
@@ -179,6 +247,34 @@ DM_HD void dm_quat_hinge_z(T& w, T& x, T& y, T& z, T s, T c) {
   T nw = w * c - z * s, nx = x * c + y * s, ny = y * c - x * s, nz = z * c + w * s;
   w = nw; x = nx; y = ny; z = nz;
 }
+
+#if defined(__CUDA_ARCH__)
+// fp32 device overloads in packed arithmetic: the quaternion travels as the pairs P = (w, x), Q = (y, z); ptxas folds the
+// half swaps, the per-half signs and the scalar broadcasts below into FFMA2 / FMUL2 operand modifiers (.LO_HI, .NP, .F32),
+// so a hinge is 2 FMUL2 + 2 FFMA2 instead of 4 FMUL + 4 FFMA.  (mju_quat2Mat in the same pairing was tried and gained nothing:
+// the scalar form only computes the entries a body's children use, and its products already contract into FMAs.)
+__device__ __forceinline__ void dm_quat_hinge_x(float& w, float& x, float& y, float& z, float s, float c) {
+  const unsigned long long C = dm_pk2(c, c);
+  const unsigned long long nP = dm_fma2(dm_pk2(x, w), dm_pk2(-s, s), dm_mul2(dm_pk2(w, x), C));
+  const unsigned long long nQ = dm_fma2(dm_pk2(z, y), dm_pk2(s, -s), dm_mul2(dm_pk2(y, z), C));
+  dm_upk2(nP, w, x);
+  dm_upk2(nQ, y, z);
+}
+__device__ __forceinline__ void dm_quat_hinge_y(float& w, float& x, float& y, float& z, float s, float c) {
+  const unsigned long long C = dm_pk2(c, c), P = dm_pk2(w, x), Q = dm_pk2(y, z);
+  const unsigned long long nP = dm_fma2(Q, dm_pk2(-s, -s), dm_mul2(P, C));
+  const unsigned long long nQ = dm_fma2(P, dm_pk2(s, s), dm_mul2(Q, C));
+  dm_upk2(nP, w, x);
+  dm_upk2(nQ, y, z);
+}
+__device__ __forceinline__ void dm_quat_hinge_z(float& w, float& x, float& y, float& z, float s, float c) {
+  const unsigned long long C = dm_pk2(c, c);
+  const unsigned long long nP = dm_fma2(dm_pk2(z, y), dm_pk2(-s, s), dm_mul2(dm_pk2(w, x), C));
+  const unsigned long long nQ = dm_fma2(dm_pk2(x, w), dm_pk2(-s, s), dm_mul2(dm_pk2(y, z), C));
+  dm_upk2(nP, w, x);
+  dm_upk2(nQ, y, z);
+}
+#endif
 
 // py3dtf Quaternion(x, y, z, w).to_rpy() of a UNIT quaternion (see oracle/rotations.py:to_rpy)
 template <typename T>

@@ -167,6 +167,8 @@ def emit_fk(m, cfg, e):
     e("    T s2x = T(0), s2y = T(0), s2z = T(0);  // sum R * (m * ipos)")
     emit_body_tail(1)
     chain_w = {}  # body -> names of (wx, wy, wz) angular contribution of its hinges
+    hinge_order = [j for i in range(2, nb) for j in range(int(m.body_jntadr[i]), int(m.body_jntadr[i] + m.body_jntnum[i]))]
+    sincos_done = set()
     for i in range(2, nb):
         p = int(m.body_parentid[i])
         e("    // body %d '%s' (parent %d)" % (i, m.body_names[i], p))
@@ -209,6 +211,17 @@ def emit_fk(m, cfg, e):
                 raise NotImplementedError("hinge axis must be a coordinate axis")
             sign = 1.0 if ax[k] > 0 else -1.0
             qa = int(m.jnt_qposadr[j])
+            # half-angle sine / cosine: consecutive hinges (emission order) in pairs, one packed evaluation for both
+            # (dm_sincos_half2, dm_math.cuh); the second hinge of a pair finds its values already there
+            if j not in sincos_done:
+                nxt = hinge_order[hinge_order.index(j) + 1] if hinge_order.index(j) + 1 < len(hinge_order) else None
+                if nxt is not None and nxt not in sincos_done:
+                    e("    T sh_%d, ch_%d, sh_%d, ch_%d; dm_sincos_half2(in.qpos(%d), in.qpos(%d), sh_%d, ch_%d, sh_%d, ch_%d);"
+                      % (j, j, nxt, nxt, qa, int(m.jnt_qposadr[nxt]), j, j, nxt, nxt))
+                    sincos_done.update((j, nxt))
+                else:
+                    e("    T sh_%d, ch_%d; dm_sincos_half(in.qpos(%d), sh_%d, ch_%d);" % (j, j, qa, j, j))
+                    sincos_done.add(j)
             e("    {  // hinge %d '%s' axis %s%s" % (j, m.jnt_names[j], "+" if sign > 0 else "-", "xyz"[k]))
             if on_chain:
                 da = int(m.jnt_dofadr[j])
@@ -216,9 +229,7 @@ def emit_fk(m, cfg, e):
                 e("      T dv_ = %sin.qvel(%d);" % ("" if sign > 0 else "-", da))
                 e("      wx_%d = dm_fma(ax_, dv_, wx_%d); wy_%d = dm_fma(ay_, dv_, wy_%d); wz_%d = dm_fma(az_, dv_, wz_%d);"
                   % (i, i, i, i, i, i))
-            e("      T s_, c_; dm_sincos_half(in.qpos(%d), s_, c_);" % qa)
-            if sign < 0:
-                e("      s_ = -s_;")
+            e("      T s_ = %ssh_%d, c_ = ch_%d;" % ("-" if sign < 0 else "", j, j))
             e("      dm_quat_hinge_%s(qw_%d, qx_%d, qy_%d, qz_%d, s_, c_);" % ("xyz"[k], i, i, i, i))
             e("    }")
         emit_body_tail(i)
