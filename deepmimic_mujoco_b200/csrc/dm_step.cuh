@@ -95,10 +95,9 @@ template <int KIND, class Rb, class IO>
 DM_HD void write_obs_tail(IO& io, float roll, float pitch, float yaw, const float* cvel, uint32_t contact, int frame, int len,
                           int clip, float& mx, float& mn) {
   using L = ObsLayout<KIND, Rb>;
-  auto put = [&](int j, float v) {
+  auto put = [&](int j, float v) {  // `max(obs) > 100 or min(obs) < -100` is `max |obs| > 100`: one NaN-propagating max per entry
     io.obs(j, v);
-    mx = dm_max_nan(mx, v);
-    mn = dm_min_nan(mn, v);
+    mx = dm_max_nan(mx, fabsf(v));
   };
   float sy, cy;
   dm_sincos_f(-yaw, sy, cy);
@@ -139,10 +138,9 @@ template <int KIND, class Rb, class IO>
 DM_HD void write_obs(IO& io, const FkOut<float>& fk, const float* root_rpy, uint32_t contact, int frame, int len,
                      int clip, float& omax, float& omin) {
   float mx = -INFINITY, mn = INFINITY;
-  auto put = [&](int j, float v) {
+  auto put = [&](int j, float v) {  // `max(obs) > 100 or min(obs) < -100` is `max |obs| > 100`: one NaN-propagating max per entry
     io.obs(j, v);
-    mx = dm_max_nan(mx, v);
-    mn = dm_min_nan(mn, v);
+    mx = dm_max_nan(mx, fabsf(v));
   };
 #pragma unroll
   for (int j = 0; j < Rb::NJ; ++j) put(j, io.qpos(7 + j));
@@ -251,7 +249,7 @@ DM_HD float imitation_reward(const IO& io, const FkOut<float>& fk, const float* 
         e_q += d;
         mx = dm_max_nan(mx, d);
         e_v += fabsf(tv.v[u] - io.qvel(Rb::sel_q(k) - 1));
-        nlim += (q <= Rb::lim_lo(k)) + (q >= Rb::lim_hi(k));
+        nlim += (q <= Rb::lim_lo(k) || q >= Rb::lim_hi(k)) ? 1 : 0;  // lo < hi: at most one of the two holds
       }
     }
   }

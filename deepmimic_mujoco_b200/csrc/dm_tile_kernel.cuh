@@ -459,12 +459,20 @@ __global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_co
         if (c <= DIM) {  // column DIM is the reward
           const float* src = c < DIM ? buf + warp * DIM + c : s_rw + warp;
           const int stride = c < DIM ? TC::NW * DIM : TC::NW;
+          // two rows per packed add / fma (FADD2 / FFMA2): 4 instructions per pair of values instead of 6
+          unsigned long long a2 = 0ull, q2 = 0ull;
+          static_assert((TE / TC::NW) % 2 == 0, "rows in pairs");
 #pragma unroll 8
-          for (int r = 0; r < TE / TC::NW; ++r) {
-            const float v = src[r * stride];
-            cs32[it] += v;
-            css32[it] = fmaf(v, v, css32[it]);
+          for (int r = 0; r < TE / TC::NW; r += 2) {
+            const unsigned long long v2 = dm_pk2(src[r * stride], src[(r + 1) * stride]);
+            a2 = dm_add2(a2, v2);
+            q2 = dm_fma2(v2, v2, q2);
           }
+          float lo, hi;
+          dm_upk2(a2, lo, hi);
+          cs32[it] = lo + hi;
+          dm_upk2(q2, lo, hi);
+          css32[it] = lo + hi;
         }
       }
 #pragma unroll
