@@ -254,8 +254,9 @@ DM_HD void dm_quat_hinge_z(T& w, T& x, T& y, T& z, T s, T c) {
 #if defined(__CUDA_ARCH__)
 // fp32 device overloads in packed arithmetic: the quaternion travels as the pairs P = (w, x), Q = (y, z); ptxas folds the
 // half swaps, the per-half signs and the scalar broadcasts below into FFMA2 / FMUL2 operand modifiers (.LO_HI, .NP, .F32),
-// so a hinge is 2 FMUL2 + 2 FFMA2 instead of 4 FMUL + 4 FFMA.  (mju_quat2Mat in the same pairing was tried and gained nothing:
-// the scalar form only computes the entries a body's children use, and its products already contract into FMAs.)
+// so a hinge is 2 FMUL2 + 2 FFMA2 instead of 4 FMUL + 4 FFMA.  (mju_quat2Mat in the same pairing was tried twice: nothing for
+// humanoid3d -- the scalar form only computes the entries a body's children use, and its products already contract into
+// FMAs -- and for unitree_g1's 38 full matrices 104 instructions fewer but SLOWER: G1 combined SoA, 1 M envs 250 -> 267 us.)
 __device__ __forceinline__ void dm_quat_hinge_x(float& w, float& x, float& y, float& z, float s, float c) {
   const unsigned long long C = dm_pk2(c, c);
   const unsigned long long nP = dm_fma2(dm_pk2(x, w), dm_pk2(-s, s), dm_mul2(dm_pk2(w, x), C));
