@@ -153,7 +153,9 @@ struct KernelGroups<Robot_unitree_g1> {  // 37 hinges: the joint blocks alone ar
   static constexpr int G = 3 * 128 / DM_TE;  // measured at 1 M envs: G = 3 (168 regs) 407 us, G = 2 (254 regs, no spills) 484 us, G = 4 (128 regs) 462 us
   // two wide groups against three capped ones: 65536 envs 29.1 vs 33.2 us, 131072 envs 52.7 vs 53.2, 262144 envs 87.0 vs 91.4,
   // 1 M envs 320 vs 308 (a lookahead slot beside the two wide groups is far slower: 108 us at 262144 envs)
-  static constexpr int GWIDE = 2, WIDE_WANT = 16;
+  // (after the packed-arithmetic changes of round 2 the two wide groups also win at 524288 envs: combined 157.3 -> 147.9 us,
+  // DPEnv 138.6 -> 137.0; at 1 M envs combined 294.2 -> 290.7 but DPEnv 256.8 -> 269.2, so the switch stays below 1 M)
+  static constexpr int GWIDE = 2, WIDE_WANT = 32;
   static constexpr int GMID = 0, MID_WANT_LO = 0, MID_WANT_HI = 0, MID_NBUF = 0;  // no middle shape
 };
 
