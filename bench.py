@@ -34,15 +34,15 @@ def _t(name, rd, wr):
     return (rd + wr, "profiles/r02_%s_ncu_full_summary.txt" % name)
 
 
-NCU_TRAFFIC = {("humanoid3d", 0, 4096, "aos"): _t("h4096", 1.769472e6, 0.0),
-               ("humanoid3d", 0, 8192, "aos"): _t("c3_8192", 3.487744e6, 0.0),
-               ("humanoid3d", 0, 65536, "aos"): _t("c3_65536", 26.884608e6, 0.460544e6),
-               ("humanoid3d", 0, 1048576, "aos"): _t("h1M", 427.973120e6, 364.157952e6),
-               ("unitree_g1", 1, 32768, "aos"): _t("g1c_32768", 15.309824e6, 0.0),
-               ("unitree_g1", 1, 262144, "aos"): _t("g1c_262144", 120.824576e6, 97.478656e6),
-               ("unitree_g1", 1, 1048576, "aos"): _t("g1c_1M", 482.838528e6, 534.682112e6),
-               ("humanoid3d", 0, 1048576, "soa"): _t("soa_h1M", 428.956928e6, 366.176256e6),
-               ("unitree_g1", 1, 1048576, "soa"): _t("soa_g1c_1M", 482.617344e6, 535.082752e6)}
+NCU_TRAFFIC = {("humanoid3d", 0, 4096, "aos"): _t("h4096", 1.769728e6, 0.000000e6),
+               ("humanoid3d", 0, 8192, "aos"): _t("c3_8192", 3.488512e6, 0.000000e6),
+               ("humanoid3d", 0, 65536, "aos"): _t("c3_65536", 26.884864e6, 0.221696e6),
+               ("humanoid3d", 0, 1048576, "aos"): _t("h1M", 444.581888e6, 362.651392e6),
+               ("unitree_g1", 1, 32768, "aos"): _t("g1c_32768", 15.305216e6, 0.000000e6),
+               ("unitree_g1", 1, 262144, "aos"): _t("g1c_262144", 120.935168e6, 95.656704e6),
+               ("unitree_g1", 1, 1048576, "aos"): _t("g1c_1M", 535.478528e6, 536.336384e6),
+               ("humanoid3d", 0, 1048576, "soa"): _t("soa_h1M", 447.850752e6, 366.636800e6),
+               ("unitree_g1", 1, 1048576, "soa"): _t("soa_g1c_1M", 524.789504e6, 535.347200e6)}
 
 
 def parse():
