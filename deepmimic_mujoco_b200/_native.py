@@ -74,7 +74,7 @@ SYMBOLS = ["dm_abi_version", "dm_create", "dm_destroy", "dm_last_error", "dm_get
            "dm_set_timing", "dm_set_kernel_variant", "dm_set_contact_mode", "dm_set_host_mode", "dm_policy_upload", "dm_policy_set_normalizer",
            "dm_policy_normalizer_from_stats", "dm_policy_act", "dm_set_policy_variant", "dm_batch_stats_noalloc",
            "dm_stats_peer_export", "dm_stats_peer_import", "dm_stats_allreduce", "dm_stats_snapshot", "dm_stats_commit", "dm_stats_read_total",
-           "dm_stats_set_auto", "dm_stats_join"]
+           "dm_stats_set_auto", "dm_stats_join", "dm_obs_abspos"]
 IPC_HANDLE_BYTES = 64
 NOALLOC_MAX_OBS_DIM, NOALLOC_MAX_ENVS = 125, 1 << 22
 
@@ -129,6 +129,7 @@ def lib():
     L.dm_stats_set_auto.argtypes = [C.c_void_p, C.c_int32]
     L.dm_stats_join.argtypes = [C.c_void_p, C.c_void_p]
     L.dm_batch_stats_noalloc.argtypes = [C.c_int, C.c_int32, C.c_int32] + [C.c_void_p] * 7
+    L.dm_obs_abspos.argtypes = [C.c_void_p, C.c_int32] + [C.c_void_p] * 8
     _lib = L
     return L
 

@@ -22,7 +22,11 @@ class DPCombinedEnv:
         self.robot = "unitree_g1"
         self.robot_config = RobotConfig(robot=self.robot)
         self.model = load_model(self.robot)
-        self._vec = DPVecEnv(1, combined=True, device=device, physics=physics, info_terms=True)
+        if self.ENV_CFG.ADD_JOINT_FORCE_OBS:
+            raise NotImplementedError("ADD_JOINT_FORCE_OBS (deepmimic_env.py:123-131) needs qfrc_unc / qfrc_constraint of MuJoCo's solver, "
+                                      "which is outside this package")
+        self._vec = DPVecEnv(1, combined=True, device=device, physics=physics, info_terms=True,
+                             add_abspos_obs=self.ENV_CFG.ADD_ABSPOS_OBS)
         self.walk_mocap, self.run_mocap, self.getup_mocap = self._vec.hp.mocaps
         self.action_space = self._vec.action_space
         self.observation_space = self._vec.observation_space
@@ -70,8 +74,9 @@ class DPCombinedEnv:
         v.qpos = np.ascontiguousarray(q, dtype=np.float32).copy()
         v.qvel = np.ascontiguousarray(qd, dtype=np.float32).copy()
         c = None if c is None else np.ascontiguousarray(c, dtype=np.uint32)
-        v.hp.step_host(1, v.qpos, v.qvel, np.ascontiguousarray(a[None]), c, v.idx, v.ep_len, v.clip, v.obs, v.reward, v.done,
+        v.hp.step_host(1, v.qpos, v.qvel, np.ascontiguousarray(a[None]), c, v.idx, v.ep_len, v.clip, v._std_obs(), v.reward, v.done,
                        v.reason, v.torque, v.terms, v.ep_return)
+        v._after_direct_step()
         self._pull()
         reason = int(v.reason[0])
         if reason == 8:

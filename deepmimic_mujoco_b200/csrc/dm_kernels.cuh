@@ -130,6 +130,64 @@ struct ResetParams {
   ClipSet cs;
 };
 
+// ---- K8: get_abspos_obs (deepmimic_env.py:133-137, ENV_CFG.ADD_ABSPOS_OBS -- off in every configuration the reference
+// ships, so this is an opt-in POST-PASS and the step kernels stay as they are).  The extended row is
+//   [ obs[0 : PHASE] | geom_xpos.flatten() (3 NGEOM) | obs[PHASE : DIM] ]
+// (the reference concatenates position, velocity, torso, contacts, joint_force, abs_pos, phase, player action).  In step
+// mode (reward != NULL) the observation-bounds guard (deepmimic_env.py:465-476) is re-evaluated over the new block: a geom
+// further than 100 m from the origin ends the episode with (obs * 0, 0, True, {}) exactly like an out-of-range standard
+// entry; a row the step kernel has already zeroed gets its new block zeroed too.
+struct AbsPosParams {
+  int n;
+  const float* qpos;     // [n, nq] row-major
+  const float* obs_in;   // [n, DIM] the step's / reset's observation
+  float* obs_out;        // [n, DIM + 3 NGEOM]
+  float* reward;         // step mode: [n], else NULL (reset mode: rows are only extended)
+  uint8_t* done;
+  uint8_t* reason;
+  const uint8_t* mask;   // NULL or [n]: rows to (re)compute
+};
+struct AbsPosIO {
+  const float* __restrict__ qp;
+  __device__ __forceinline__ float qpos(int j) const { return __ldg(qp + j); }
+  __device__ __forceinline__ float qvel(int) const { return 0.0f; }
+};
+struct AbsPosSink {
+  static constexpr bool kWantsGeoms = true;
+  __device__ static constexpr bool contact_on() { return false; }
+  float* __restrict__ out;  // this row's geom block
+  float m;                  // max |coordinate|, NaN-propagating like numpy's max / min
+  template <typename T> __device__ __forceinline__ void body(int, T, T, T) {}
+  __device__ __forceinline__ void geom(int g, float x, float y, float z) {
+    out[3 * g] = x; out[3 * g + 1] = y; out[3 * g + 2] = z;
+    m = dm_max_nan(m, dm_max_nan(fabsf(x), dm_max_nan(fabsf(y), fabsf(z))));
+  }
+};
+template <int KIND, class Rb>
+__global__ void __launch_bounds__(128) obs_abspos_kernel(const AbsPosParams p) {
+  using OL = ObsLayout<KIND, Rb>;
+  constexpr int NG3 = 3 * Rb::NGEOM, EXT = OL::DIM + NG3;
+  const int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= p.n || (p.mask && !p.mask[env])) return;
+  const float* __restrict__ src = p.obs_in + (size_t)env * OL::DIM;
+  float* __restrict__ dst = p.obs_out + (size_t)env * EXT;
+  for (int j = 0; j < OL::PHASE; ++j) dst[j] = src[j];
+  for (int j = OL::PHASE; j < OL::DIM; ++j) dst[NG3 + j] = src[j];
+  AbsPosSink sink{dst + OL::PHASE, 0.0f};
+  for (int j = 0; j < NG3; ++j) sink.out[j] = 0.0f;  // the world body's geoms (the floor plane at the origin)
+  AbsPosIO in{p.qpos + (size_t)env * Rb::NQ};
+  FkOut<float> o;
+  Rb::template fk<float>(in, o, sink);
+  if (!p.reward) return;
+  const bool already = p.reason && p.reason[env] == R_OBS_BOUNDS;
+  if (already || sink.m > 100.0f) {
+    for (int j = 0; j < EXT; ++j) dst[j] = dst[j] * 0.0f;  // `_get_obs() * 0.`: an infinite entry becomes NaN
+    p.reward[env] = 0.0f;
+    p.done[env] = 1;
+    if (p.reason) p.reason[env] = R_OBS_BOUNDS;
+  }
+}
+
 struct ResetIO {
   const float* __restrict__ row;  // state row: qpos | qvel
   float* __restrict__ ob;

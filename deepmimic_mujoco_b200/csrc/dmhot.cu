@@ -1525,6 +1525,28 @@ extern "C" int dm_batch_stats_noalloc(int device, int32_t n, int32_t obs_dim, co
   return DM_OK;
 }
 
+// ---- get_abspos_obs as an opt-in post-pass (K8, dm_kernels.cuh) -----------------------------------------------------
+extern "C" int dm_obs_abspos(dm_handle* h, int32_t n, const float* qpos, const float* obs_in, float* obs_out, float* reward,
+                             uint8_t* done, uint8_t* reason, const uint8_t* mask, void* stream) {
+  if (!h) return fail(nullptr, DM_E_ARG, "dm_obs_abspos: NULL handle");
+  if (n < 0 || (n > 0 && (!qpos || !obs_in || !obs_out))) return fail(h, DM_E_ARG, "dm_obs_abspos: a required buffer is NULL (qpos obs_in obs_out)");
+  if (reward && !done) return fail(h, DM_E_ARG, "dm_obs_abspos: step mode (reward given) needs the done flags");
+  if (obs_in == obs_out) return fail(h, DM_E_ARG, "dm_obs_abspos: the extended rows are wider than the input rows: not in place");
+  if (n == 0) return DM_OK;
+  CU(h, cudaSetDevice(h->device));
+  AbsPosParams p{n, qpos, obs_in, obs_out, reward, done, reason, mask};
+  int rc = dispatch(h, [&](auto rb, auto kind) -> int {
+    using Rb = decltype(rb);
+    constexpr int KIND = decltype(kind)::value;
+    obs_abspos_kernel<KIND, Rb><<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(p);
+    return DM_OK;
+  });
+  if (rc) return rc;
+  CU(h, cudaGetLastError());
+  h->launches++;
+  return DM_OK;
+}
+
 // ---- the statistics collective (K7, dm_peer.cuh) ------------------------------------------------------------------------
 static int peer_ensure(dm_handle* h) {  // device buffers of the collective, allocated on first use
   if (h->d_total) return DM_OK;

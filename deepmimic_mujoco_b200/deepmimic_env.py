@@ -27,7 +27,11 @@ class DPEnv:
         self.motion_config = MotionConfig(motion=motion, robot=robot)
         self.robot_config = RobotConfig(robot=robot)
         self.model = load_model(robot)
-        self._vec = DPVecEnv(1, self.motion_config.motion, robot, device=device, physics=physics, info_terms=True)
+        if self.ENV_CFG.ADD_JOINT_FORCE_OBS:
+            raise NotImplementedError("ADD_JOINT_FORCE_OBS (deepmimic_env.py:123-131) needs qfrc_unc / qfrc_constraint of MuJoCo's solver, "
+                                      "which is outside this package")
+        self._vec = DPVecEnv(1, self.motion_config.motion, robot, device=device, physics=physics, info_terms=True,
+                             add_abspos_obs=self.ENV_CFG.ADD_ABSPOS_OBS)
         self.mocap = self._vec.hp.mocaps[0]
         self.mocap_dt = self.mocap.dt
         self.mocap_data_len = self.mocap.get_length()
@@ -35,6 +39,8 @@ class DPEnv:
         # step() returns (obs, 0, False, {}) before any reward / termination / counter logic (:394-395).  The kernel still
         # needs a table to index, so the motion's clip stays loaded underneath; only this view hides it.
         self._no_mocap = not load_mocap
+        if self._no_mocap and self._vec.add_abspos_obs:
+            raise NotImplementedError("load_mocap=False together with ADD_ABSPOS_OBS is not provided")
         if self._no_mocap:
             self.mocap = SimpleNamespace(data_config=None, data_vel=None, data_body_xpos=None, data_geom_xpos=None, dt=None)
             self.mocap_dt = None
@@ -120,8 +126,9 @@ class DPEnv:
                   None if c is None else np.ascontiguousarray(c, dtype=np.uint32))
         v.qpos, v.qvel = np.ascontiguousarray(fs[0]).copy(), np.ascontiguousarray(fs[1]).copy()
         contact = fs[2] if len(fs) > 2 else None
-        v.hp.step_host(n, v.qpos, v.qvel, v._actions, contact, v.idx, v.ep_len, v.clip, v.obs, v.reward, v.done, v.reason,
+        v.hp.step_host(n, v.qpos, v.qvel, v._actions, contact, v.idx, v.ep_len, v.clip, v._std_obs(), v.reward, v.done, v.reason,
                        v.torque, v.terms, v.ep_return)
+        v._after_direct_step()
         self._pull()
         self.sim.data.time += self.model.timestep
         reason = int(v.reason[0])

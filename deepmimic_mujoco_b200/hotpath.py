@@ -375,6 +375,18 @@ class HotPath:
         N.check(self.L.dm_stats_read_total(self.h, N.np_ptr(out), stream), self.h, "dm_stats_read_total")
         return out
 
+    def obs_abspos(self, n, qpos, obs_in, obs_out, reward=None, done=None, reason=None, mask=None, stream=None):
+        """get_abspos_obs (deepmimic_env.py:133-137) as a post-pass over DEVICE-accessible buffers (torch CUDA tensors, or
+        the handle's pinned host block): obs_out[e] = [obs_in[e][:phase], geom_xpos(qpos[e]).flatten(), obs_in[e][phase:]].
+        With reward / done (/ reason) the observation-bounds guard is applied to the new block (step mode)."""
+        p = self._ptr
+        N.check(self.L.dm_obs_abspos(self.h, int(n), p(qpos), p(obs_in), p(obs_out), p(reward), p(done), p(reason), p(mask), stream),
+                self.h, "dm_obs_abspos")
+
+    @property
+    def abspos_dim(self):
+        return 3 * self.dims.ngeom
+
     def launch_count(self):
         k = C.c_int64()
         N.check(self.L.dm_launch_count(self.h, C.byref(k)), self.h, "dm_launch_count")

@@ -157,8 +157,13 @@ class _OutputRing:
 
 class DPVecEnv(_vecenv_base()):
     def __init__(self, num_envs, motion="walk", robot="humanoid3d", combined=False, device=0, seed=0, physics=None,
-                 info_terms=False, copy_outputs=True, contact_from_fk=False, timelimit_truncated=False, pin_cpus=None):
+                 info_terms=False, copy_outputs=True, contact_from_fk=False, timelimit_truncated=False, pin_cpus=None,
+                 add_abspos_obs=False):
         self.num_envs = int(num_envs)
+        # ENV_CFG.ADD_ABSPOS_OBS (deepmimic_env.py:133-137; False in every configuration the reference ships): the
+        # observation grows by geom_xpos.flatten() in front of the phase entry.  An opt-in post-pass (dm_obs_abspos) behind
+        # the step / reset kernels; the default path is untouched.
+        self.add_abspos_obs = bool(add_abspos_obs)
         # pin_cpus: the CPUs this process (and the copy helper threads the library starts later, which inherit the mask)
         # may run on.  "auto" under a one-process-per-GPU launcher (LOCAL_RANK / LOCAL_WORLD_SIZE) gives every rank its own
         # contiguous slice of the cores, so that N ranks staging their batches at the same time do not share cores
@@ -182,6 +187,7 @@ class DPVecEnv(_vecenv_base()):
             self.hp.load_motions(self.motions)
         self.hp.set_contact_mode(contact_from_fk)
         d = self.hp.dims
+        self.obs_dim = d.obs_dim + (3 * d.ngeom if self.add_abspos_obs else 0)
         mc = self.hp.model_constants()
         lo, hi = mc["ctrl_lo"][:d.na].copy(), mc["ctrl_hi"][:d.na].copy()
         if self.combined:  # combined_env.py:194-200: ctrlrange / ACT_SCALE
@@ -189,10 +195,10 @@ class DPVecEnv(_vecenv_base()):
         GymBox = _gym_box()
         if type(self).__mro__[1] is not object and GymBox is not None:  # a real SB3 VecEnv wants real gym spaces
             act_space = GymBox(low=lo, high=hi, dtype=np.float32)
-            obs_space = GymBox(low=-np.inf, high=np.inf, shape=(d.obs_dim,), dtype=np.float32)
+            obs_space = GymBox(low=-np.inf, high=np.inf, shape=(self.obs_dim,), dtype=np.float32)
         else:
             act_space = Box(lo, hi)
-            obs_space = Box(np.full(d.obs_dim, -np.inf), np.full(d.obs_dim, np.inf))
+            obs_space = Box(np.full(self.obs_dim, -np.inf), np.full(self.obs_dim, np.inf))
         if type(self).__mro__[1] is not object:
             super().__init__(self.num_envs, obs_space, act_space)
         self.action_space, self.observation_space = act_space, obs_space
@@ -212,7 +218,7 @@ class DPVecEnv(_vecenv_base()):
         self.obs, self.reward, self.done, self.reason = pin["obs"], pin["reward"], pin["done"], pin["reason"]
         self.torque = pin["torque"]
         self.terms = pin.get("terms")
-        self.terminal_obs = np.zeros((n, d.obs_dim), np.float32)
+        self.terminal_obs = np.zeros((n, self.obs_dim), np.float32)
         self._actions = None
         self._force = None
         self.h2d_bytes = self.d2h_bytes = 0
@@ -230,7 +236,12 @@ class DPVecEnv(_vecenv_base()):
         # caller-owned outputs (copy_outputs=True) come from small rings that are reused only once the caller has
         # dropped every view of a slot (see _OutputRing).  The observation slots are PINNED host memory: dm_step_host
         # then lets the kernel write the observations straight into the array the caller receives.
-        self._rings = {"obs": _OutputRing(pin["obs"].shape, np.float32, 4, True),
+        if self.add_abspos_obs:  # the extended rows and the reset mask have to be device-accessible: pinned
+            import torch
+            self._ext_keep = [torch.empty(n * self.obs_dim, dtype=torch.float32, pin_memory=True), torch.zeros(max(n, 1), dtype=torch.uint8, pin_memory=True)]
+            self._ext = self._ext_keep[0].numpy().reshape(n, self.obs_dim)
+            self._ext_mask = self._ext_keep[1].numpy()[:n]
+        self._rings = {"obs": _OutputRing((n, self.obs_dim), np.float32, 4, True),
                        "rew": _OutputRing((n,), np.float32, 4, False), "done": _OutputRing((n,), np.bool_, 4, False)}
 
     @staticmethod
@@ -292,7 +303,10 @@ class DPVecEnv(_vecenv_base()):
                 frame = np.where(frame < 0, frame + lens, frame).astype(np.int32)  # Python's negative indexing
         # always into the handle's own pinned slot: an array handed to the caller by an earlier step() is never rewritten
         obs = self._pin["obs"]
-        if mask is not None and self.obs is not obs:
+        if self.add_abspos_obs:  # the pinned slot always holds the last standard rows; keep the untouched extended rows
+            if mask is not None and self.obs is not self._ext and getattr(self.obs, "shape", None) == self._ext.shape:
+                np.copyto(self._ext, self.obs)
+        elif mask is not None and self.obs is not obs:
             np.copyto(obs, self.obs)
         self.obs = obs
         self.hp.reset_host(self.num_envs, self.idx, self.ep_len, self.clip, obs,
@@ -300,7 +314,35 @@ class DPVecEnv(_vecenv_base()):
                            frame=frame,
                            coin=None if coin is None else np.ascontiguousarray(coin, dtype=np.int32),
                            qpos=self.qpos, qvel=self.qvel, ep_return=self.ep_return, seed=self._seed, counter=self._counter)
+        if self.add_abspos_obs:
+            self._extend_obs(obs, self._ext, mask=mask)
+            self.obs = self._ext
+            return self._ext.copy()
         return obs.copy()
+
+    def _std_obs(self):
+        """Where a direct dm_step_host call (the N = 1 env classes) has to write the standard observation rows."""
+        return self._pin["obs"] if self.add_abspos_obs else self.obs
+
+    def _after_direct_step(self):
+        """... and what follows it: with ADD_ABSPOS_OBS the rows are widened and the bounds guard re-run over the new block."""
+        if self.add_abspos_obs:
+            self._extend_obs(self._pin["obs"], self._ext, step=True)
+            self.obs = self._ext
+
+    def _extend_obs(self, std_obs, ext, mask=None, step=False):
+        """dm_obs_abspos over the pinned block: ext rows = [std[:phase], geom_xpos(qpos), std[phase:]] (+ the bounds guard
+        over the new block in step mode).  Synchronous: the rows are read on the host right after."""
+        import torch
+        if self.qpos is not self._pin["qpos"]:  # the N = 1 env classes keep their own copy of the state
+            np.copyto(self._pin["qpos"], self.qpos)
+        m = None
+        if mask is not None:
+            np.copyto(self._ext_mask, np.asarray(mask).astype(np.uint8, copy=False))
+            m = self._ext_mask
+        self.hp.obs_abspos(self.num_envs, self._pin["qpos"], std_obs, ext, self.reward if step else None,
+                           self.done if step else None, self.reason if step else None, m)
+        torch.cuda.synchronize(self.device)
 
     def step_async(self, actions, force_state=None):
         actions = np.asarray(actions)
@@ -353,7 +395,12 @@ class DPVecEnv(_vecenv_base()):
         # copy_outputs: the observation goes straight into a fresh caller-owned array (copied inside dm_step_host while
         # the remaining outputs are still in flight); self.obs then aliases it until the next step
         self.obs = None  # drop last step's array: if the caller did too, _fresh hands it out again
-        out_obs = self._fresh("obs") if self.copy_outputs else p["obs"]
+        ext = None
+        if self.add_abspos_obs:  # the kernel writes the standard rows into the pinned slot; the post-pass below widens them
+            ext = self._fresh("obs") if self.copy_outputs else self._ext
+            out_obs = p["obs"]
+        else:
+            out_obs = self._fresh("obs") if self.copy_outputs else p["obs"]
         self.obs = out_obs
         a, sp, ptr = self._args, self._slot_ptr, self._args_ptr
         a.qpos = sp["qpos"] if qpos_in is p["qpos"] else ptr(qpos_in)
@@ -367,6 +414,11 @@ class DPVecEnv(_vecenv_base()):
             N.check(rc, h, "dm_step_host")
         self.qpos, self.qvel, self._actions = p["qpos"], p["qvel"], p["action"]  # the pinned copies, never the caller's arrays
         self.h2d_bytes, self.d2h_bytes = self._h2d.value, self._d2h.value
+        if ext is not None:
+            self._extend_obs(p["obs"], self._ext, step=True)  # always into the pinned rows: a ring that is fully held by the
+            if ext is not self._ext:                          # caller hands out ordinary (pageable) arrays
+                np.copyto(ext, self._ext)
+            self.obs = out_obs = ext
         if failed is not None:  # (obs * 0, 0, True, {}) and no counter advanced past the failure (deepmimic_env.py:377-378)
             self.obs[failed] = 0.0
             self.reward[failed] = 0.0
@@ -393,11 +445,15 @@ class DPVecEnv(_vecenv_base()):
             self.terminal_obs[ids] = self.obs[ids]
             self._counter += 1
             ra = self._rargs
-            ra.mask, ra.obs = self._args_ptr(dones), self._args_ptr(self.obs)
+            ra.mask, ra.obs = self._args_ptr(dones), self._args_ptr(p["obs"] if ext is not None else self.obs)
             ra.seed, ra.counter = self._seed, self._counter
             rc = self.hp.L.dm_reset_host(self.hp.h, C.byref(ra))
             if rc:
                 N.check(rc, self.hp.h, "dm_reset_host")
+            if ext is not None:
+                self._extend_obs(p["obs"], self._ext, mask=dones)
+                if ext is not self._ext:
+                    ext[ids] = self._ext[ids]
             for k, i in enumerate(ids):
                 info = infos[i]
                 info["terminal_observation"] = self.terminal_obs[i].copy()
@@ -450,6 +506,8 @@ class DPVecEnv(_vecenv_base()):
                              reason=torch.zeros(n, dtype=torch.uint8, device=dev),
                              torque=torch.zeros(n, d.nu, device=dev), terminal_obs=torch.zeros(n, d.obs_dim, device=dev),
                              qpos=t(self.qpos), qvel=t(self.qvel))
+            if self.add_abspos_obs:
+                self._dev.update(obs_ext=torch.zeros(n, self.obs_dim, device=dev), terminal_obs_ext=torch.zeros(n, self.obs_dim, device=dev))
         return self._dev
 
     def reset_tensors(self):
@@ -459,6 +517,9 @@ class DPVecEnv(_vecenv_base()):
         self._counter += 1
         self.hp.reset(self.num_envs, b["idx"], b["ep_len"], b["clip"], b["obs"], mask=None, qpos=b["qpos"], qvel=b["qvel"],
                       ep_return=b["ep_return"], seed=self._seed, counter=self._counter)
+        if self.add_abspos_obs:
+            self.hp.obs_abspos(self.num_envs, b["qpos"], b["obs"], b["obs_ext"])
+            return b["obs_ext"]
         return b["obs"]
 
     def step_tensors(self, actions, qpos, qvel, contact=None, auto_reset=True, stats=False):
@@ -469,8 +530,17 @@ class DPVecEnv(_vecenv_base()):
         n = self.num_envs
         self.hp.step(n, qpos, qvel, actions, contact, b["idx"], b["ep_len"], b["clip"], b["obs"], b["reward"], b["done"],
                      b["reason"], b["torque"], None, b["ep_return"], stats=stats)
+        if self.add_abspos_obs:  # widen the rows (and re-run the bounds guard over the new block) before anybody reads `done`
+            self.hp.obs_abspos(n, qpos, b["obs"], b["obs_ext"], b["reward"], b["done"], b["reason"])
         if auto_reset:
             self._counter += 1
+            if self.add_abspos_obs:
+                import torch
+                torch.where(b["done"].bool()[:, None], b["obs_ext"], b["terminal_obs_ext"], out=b["terminal_obs_ext"])
             self.hp.reset(n, b["idx"], b["ep_len"], b["clip"], b["obs"], mask=b["done"], qpos=b["qpos"], qvel=b["qvel"],
                           ep_return=b["ep_return"], seed=self._seed, counter=self._counter, terminal_obs=b["terminal_obs"])
+            if self.add_abspos_obs:  # the reset rows: their reference state is in b['qpos']
+                self.hp.obs_abspos(n, b["qpos"], b["obs"], b["obs_ext"], mask=b["done"])
+        if self.add_abspos_obs:
+            return b["obs_ext"], b["reward"], b["done"]
         return b["obs"], b["reward"], b["done"]

@@ -258,6 +258,21 @@ int dm_stats_join(dm_handle* h, void* stream);
 int dm_batch_stats_noalloc(int device, int32_t n, int32_t obs_dim, const float* obs, const float* reward, const uint8_t* done,
                            const float* ep_return, const int32_t* ep_len, double* out_stats, void* stream);
 
+/* dm_obs_abspos -- get_abspos_obs (src/deepmimic_env.py:133-137: `mjdata.geom_xpos.flatten()` appended to the observation
+ * when ENV_CFG.ADD_ABSPOS_OBS is set; False in every configuration the reference ships, src/deepmimic_env.py:267,
+ * src/combined_env.py:31).  An opt-in POST-PASS over device buffers, after dm_step / dm_reset on the same stream:
+ *   obs_out[e] = [ obs_in[e][0 : phase] | geom_xpos(qpos[e]) as 3 * ngeom floats | obs_in[e][phase : obs_dim] ]
+ * (the reference's concatenation order, src/deepmimic_env.py:45; the world body's floor geom is at the origin).
+ *   qpos [n, nq], obs_in [n, obs_dim], obs_out [n, obs_dim + 3 * ngeom]   row-major device pointers; not in place
+ *   reward / done / reason   step mode (reward != NULL): the observation-bounds guard (src/deepmimic_env.py:465-476) is
+ *                            applied to the new block: |coordinate| > 100 -> (obs * 0, 0, True, {}), reason = obs-bounds; a
+ *                            row the step already zeroed gets its new block zeroed too.  NULL: rows are only extended
+ *                            (after a reset).
+ *   mask     NULL or [n]: only rows with mask != 0 are written (the environments a masked reset touched)
+ * get_joint_force_obs (src/deepmimic_env.py:123-131) needs MuJoCo's constraint solver and is not provided. */
+int dm_obs_abspos(dm_handle* h, int32_t n, const float* qpos, const float* obs_in, float* obs_out, float* reward, uint8_t* done,
+                  uint8_t* reason, const uint8_t* mask, void* stream);
+
 /* launch bookkeeping for bench.py ("gpu_launches") */
 int dm_launch_count(const dm_handle* h, int64_t* kernels);
 /* name + average device time (CUDA events on the launch stream) of the step kernel since the last call

@@ -88,7 +88,7 @@ def contact_flags(model, rc, contacts):
 
 # ------------------------------------------------------------------ observation
 def observation(d, model, idx, motion_len, player_action, getup_state, cfg, rc):
-    """get_obs (deepmimic_env.py:33-45) with the default-off joint-force / abs-pos blocks omitted."""
+    """get_obs (deepmimic_env.py:33-45); the joint-force block (:123-131, default off) needs MuJoCo's solver and is omitted."""
     S = cfg.VEL_OBS_SCALE
     parts = [d.qpos[7:].copy(), d.qvel[6:] * S]
     b = model.body_name2id(rc["torso"])
@@ -107,8 +107,10 @@ def observation(d, model, idx, motion_len, player_action, getup_state, cfg, rc):
         parts.append(np.array([rf, lf]))
     if cfg.ADD_EXTRA_CONTACT_OBS:  # :107-121
         parts.append(np.array(extra))
-    if cfg.ADD_JOINT_FORCE_OBS or cfg.ADD_ABSPOS_OBS:
-        raise NotImplementedError("default-off observation blocks (deepmimic_env.py:123-137)")
+    if cfg.ADD_JOINT_FORCE_OBS:
+        raise NotImplementedError("get_joint_force_obs (deepmimic_env.py:123-131): qfrc_unc / qfrc_constraint need MuJoCo's solver")
+    if cfg.ADD_ABSPOS_OBS:  # :133-137
+        parts.append(np.array(d.geom_xpos).flatten() * 1.0)
     if cfg.ADD_PHASE_OBS:  # :139-143
         parts.append(np.array([np.clip(1.0 * idx / motion_len, 0.0, 1.0)]))
     if cfg.ADD_PLAYER_ACTION_OBS:  # :145-173
@@ -193,12 +195,13 @@ def tables_for(robot, motion):
 class SingleClipEnv:
     """DPEnv (deepmimic_env.py:273-510) driven by force_state."""
 
-    def __init__(self, motion=None, robot="humanoid3d", tables=None):
+    def __init__(self, motion=None, robot="humanoid3d", tables=None, add_abspos_obs=False):
         self.motion = "walk" if motion is None else motion
         self.robot = robot
         self.rc = ROBOTS[robot]
         self.model = load_model(robot)
         self.cfg = ObsFlags(False)
+        self.cfg.ADD_ABSPOS_OBS = bool(add_abspos_obs)
         self.mocap = tables if tables is not None else tables_for(robot, self.motion)
         self.mocap_data_len = self.mocap.get_length()
         self.act_scale = 20.0 if robot == "unitree_g1" else 1.0  # :347-349
@@ -324,11 +327,12 @@ CLIP_WALK, CLIP_RUN, CLIP_GETUP, CLIP_TO_GETUP = range(4)
 class MultiClipEnv:
     """DPCombinedEnv (combined_env.py:102-533) driven by force_state."""
 
-    def __init__(self):
+    def __init__(self, add_abspos_obs=False):
         self.robot = "unitree_g1"
         self.rc = ROBOTS[self.robot]
         self.model = load_model(self.robot)
         self.cfg = ObsFlags(True)
+        self.cfg.ADD_ABSPOS_OBS = bool(add_abspos_obs)
         self.walk_mocap = tables_for(self.robot, "walk")
         self.run_mocap = tables_for(self.robot, "run")
         self.getup_mocap = tables_for(self.robot, "getup_facedown_towalk")

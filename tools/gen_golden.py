@@ -235,7 +235,7 @@ def run_combined(name, script, seed):
     for st in script:
         reset = st.get("reset")  # (rsi, coin, frame)
         code = -1
-        reset_obs = np.full(98, np.nan)
+        reset_obs = np.full(env.observation_space.shape[0], np.nan)
         if reset is not None:
             rsi, coin, frame = reset
             draws = [coin, frame]
@@ -303,6 +303,33 @@ def combined_scenarios():
 
 
 # ----------------------------------------------------------------------------- loader and math
+def abspos_goldens():
+    """ENV_CFG.ADD_ABSPOS_OBS = True (deepmimic_env.py:133-137; off in every configuration the reference ships): the
+    observation grows by geom_xpos.flatten() in front of the phase entry.  Short trajectories of both env classes with a
+    reset, a state whose geoms leave the +-100 m box (the observation-bounds guard fires on the NEW block only) and a
+    state that trips the guard through a standard entry."""
+    out = {}
+
+    def far(q, v):
+        q[0] = 150.0   # root x: every geom is > 100 m from the origin, no standard entry is out of range
+
+    def fast(q, v):
+        v[8] = 1500.0  # a joint velocity: 0.1 * 1500 > 100 in the standard block
+
+    ref_dp.DPEnv.ENV_CFG.ADD_ABSPOS_OBS = True
+    ref_cb.DPCombinedEnv.ENV_CFG.ADD_ABSPOS_OBS = True
+    try:
+        steps = [{"reset": 12}] + [{} for _ in range(9)] + [{"edit": far}, {"reset": 3}, {}, {"edit": fast}, {"reset": 20}] + [{} for _ in range(5)]
+        out.update(run_dpenv("h_walk_abspos", "humanoid3d", "walk", steps, 71, 1.0))
+        out.update(run_dpenv("g1_walk_abspos", "unitree_g1", "walk", steps, 72, 0.5))
+        csteps = [{"reset": (True, 0, 40)}] + [{} for _ in range(7)] + [{"edit": far}, {"reset": (True, 1, 10)}, {}, {}]
+        out.update(run_combined("c_abspos", csteps, 73))
+    finally:
+        ref_dp.DPEnv.ENV_CFG.ADD_ABSPOS_OBS = False
+        ref_cb.DPCombinedEnv.ENV_CFG.ADD_ABSPOS_OBS = False
+    return out
+
+
 def loader_goldens():
     out = {}
     clips = [("humanoid3d", "walk", 1), ("humanoid3d", "run", 1), ("humanoid3d", "spinkick", 1),
@@ -348,11 +375,13 @@ def main():
         dp = dpenv_scenarios()
         cb = combined_scenarios()
         ld = loader_goldens()
+        ab = abspos_goldens()
     mt = math_goldens()
     np.savez_compressed(os.path.join(OUT, "dpenv_steps.npz"), **dp)
     np.savez_compressed(os.path.join(OUT, "combined_steps.npz"), **cb)
     np.savez_compressed(os.path.join(OUT, "loader_tables.npz"), **ld)
     np.savez_compressed(os.path.join(OUT, "math_gohlke.npz"), **mt)
+    np.savez_compressed(os.path.join(OUT, "abspos_steps.npz"), **ab)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
     for k in sorted(dp):
