@@ -114,7 +114,7 @@ struct TileCfg {
   static constexpr size_t ACC_BYTES = sizeof(double) * (2 * NCOLIT * TE + 4);  // per group, STATS only
   static constexpr int MAXBUF = 12;                                            // ring slots (mbarriers 0 .. MAXBUF-1, table = MAXBUF)
   static constexpr int NUP = (Rb::NU + 3) / 4 * 4;
-  static constexpr size_t FIXED_BYTES = 128 + sizeof(float) * 3 * NUP;  // mbarriers + motor table (gear | lo | hi)
+  static constexpr size_t FIXED_BYTES = 128 + sizeof(float) * 3 * NUP + 64;  // mbarriers + motor table (gear | lo | hi) + issued[16]
   static_assert(FIXED_BYTES % 16 == 0 && BUF_BYTES % 128 == 0, "alignment");
   static constexpr size_t SMEM_BUDGET = 227 * 1024;
 };
@@ -146,7 +146,9 @@ struct KernelGroups {  // measured on humanoid3d: G = 5 (96 registers, ~330 B of
   static constexpr int GWIDE = 2, WIDE_WANT = 4;
   // in between, three groups at 164 registers (no spills) plus ONE lookahead ring slot beat four capped groups:
   // 262144 envs 52.2 vs 55.5 us, 524288 envs 91.0 vs 94.8, 1 M envs 168.1 vs 172.7; at 4 M envs 639 vs 634 (four groups again)
-  static constexpr int GMID = 3, MID_WANT_LO = 8, MID_WANT_HI = 80, MID_NBUF = 4;
+  // (after the instruction cuts of round 2 the middle shape also wins beyond 80 tiles per SM: 2 M envs 313 -> 280 us = 0.91,
+  // so it has no upper bound any more; DM_MID_HI restores one)
+  static constexpr int GMID = 3, MID_WANT_LO = 8, MID_WANT_HI = 1 << 30, MID_NBUF = 4;
 };
 template <>
 struct KernelGroups<Robot_unitree_g1> {  // 37 hinges: the joint blocks alone are 74 live registers when the tile is written
@@ -190,6 +192,15 @@ __global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_co
   extern __shared__ __align__(128) unsigned char smem_raw[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);      // [0..MAXBUF) ring-slot barriers, [MAXBUF] table barrier
   float* s_motor = reinterpret_cast<float*>(smem_raw + 128);   // [3][NUP]
+  // issued[slot] = index j of the tile whose load was issued into the slot last.  Needed when the ring has more slots than
+  // groups (the middle shape): consecutive tenants of a slot are then consumed by DIFFERENT groups, and a consumer that
+  // reached its parity wait before the previous tenant's load had even completed would be let through at once
+  // (mbarrier.try_wait.parity takes the parity of the immediately PRECEDING phase for "complete"), work on stale data and
+  // corrupt the barrier's transaction count: an `unspecified launch failure` after some thousands of tiles, first seen as
+  // a failure after 21-23 consecutive steps of 1 M environments in an experimental build and reproducible with the
+  // shipped arithmetic at 2-4 M environments.  A consumer therefore first waits until its tile's load has been ISSUED --
+  // which the previous consumer of the slot does after it has finished with the slot -- and only then on the parity.
+  volatile int* s_issued = reinterpret_cast<volatile int*>(smem_raw + 128 + sizeof(float) * 3 * TC::NUP);
   float* s_table = reinterpret_cast<float*>(smem_raw + TC::FIXED_BYTES);
   const int n_groups = blockDim.x / TE, nbuf = x.nbuf;
   const int tid = threadIdx.x, group = tid / TE, gt = tid % TE, lane = tid & 31, warp = gt >> 5;
@@ -216,12 +227,15 @@ __global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_co
     tma_load_1d(dst, p.qpos + f0 * Rb::NQ, sizeof(float) * TE * Rb::NQ, bars + slot);
     tma_load_1d(dst + TE * Rb::NQ, p.qvel + f0 * Rb::NV, sizeof(float) * TE * Rb::NV, bars + slot);
     if (act) tma_load_1d(dst + TE * TC::ROW, p.action + f0 * Rb::NA, sizeof(float) * TC::ACT_FLOATS, bars + slot);
+    __threadfence_block();  // the arrive above is ordered before the flag
+    s_issued[slot] = j;
   };
 
   if (tid == 0) {
     for (int g = 0; g < 16; ++g) mbar_init(bars + g, 1);
     mbar_fence_init();
   }
+  if (tid < 16) s_issued[tid] = -1;
   if (STATS) {
 #pragma unroll
     for (int k = 0; k < 2 * NCOLIT; ++k) my_acc[k * TE] = 0.0;
@@ -387,6 +401,10 @@ __global__ void __launch_bounds__(DM_TE * G, 1) step_tile_kernel(const __grid_co
     if (!table_ready) {
       mbar_wait(bars + TC::MAXBUF, 0);
       table_ready = true;
+    }
+    if (nbuf != n_groups) {  // see s_issued above
+      while (s_issued[slot] < j) __nanosleep(32);
+      __threadfence_block();
     }
     mbar_wait(bars + slot, parity);
     // the tile this slot receives next, towards L2 while this one is computed: its TMA load then finds it there (measured:

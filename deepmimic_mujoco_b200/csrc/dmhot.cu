@@ -619,7 +619,9 @@ static int launch_step(dm_handle* h, const dm_step_args* a, cudaStream_t s) {
       if (wide && G > KernelGroups<Rb>::GWIDE) G = KernelGroups<Rb>::GWIDE;
       // ... and some robots have a middle shape (KernelGroups::GMID groups without a register cap plus a lookahead slot)
       using KG = KernelGroups<Rb>;
-      const bool mid = !wide && !a->terms && KG::GMID > 0 && h->wide_override != 0 && want >= KG::MID_WANT_LO && want <= KG::MID_WANT_HI &&
+      static const int mid_hi_env = getenv("DM_MID_HI") ? atoi(getenv("DM_MID_HI")) : 0;
+      const int mid_hi = mid_hi_env > 0 ? mid_hi_env : KG::MID_WANT_HI;
+      const bool mid = !wide && !a->terms && KG::GMID > 0 && h->wide_override != 0 && want >= KG::MID_WANT_LO && want <= mid_hi &&
                        G >= KG::GMID && h->max_groups_override == 0 && h->nbuf_override == 0 &&
                        table_bytes + KG::MID_NBUF * TC::BUF_BYTES + KG::GMID * acc_bytes <= avail;  // only with the clip table in shared memory
       if (mid) G = KG::GMID;

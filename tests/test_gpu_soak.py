@@ -1,6 +1,7 @@
 """Many consecutive steps from one seeded state at a size where every SM carries dozens of tiles (1 M environments, two
-resident batches stepped in turn, statistics on): a variant of the step arithmetic once produced a launch failure after ~20
-such steps that no test of a few steps saw.  Checked: every launch completes, the statistics count is exact, the episode
+resident batches stepped in turn, statistics on).  A race between the groups of a CTA over the tenants of a ring slot
+(mbarrier parity taken for the previous phase) produced an `unspecified launch failure` only after thousands of tiles -- ~20
+steps at 1-3 M environments -- which no test of a few steps saw.  Checked: every launch completes, the statistics count is exact, the episode
 counters advanced by exactly the number of steps, nothing non-finite appears."""
 import numpy as np
 import pytest
@@ -8,12 +9,16 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("robot,combined,soa", [("humanoid3d", False, False), ("humanoid3d", False, True), ("unitree_g1", True, False)])
-def test_sixty_steps_at_one_million_envs(robot, combined, soa):
+@pytest.mark.parametrize("robot,combined,soa,n,steps", [("humanoid3d", False, False, 1 << 20, 60), ("humanoid3d", False, True, 1 << 20, 60),
+                                                         ("unitree_g1", True, False, 1 << 20, 60),
+                                                         # 3 M envs in the middle launch shape (3 groups, 4 ring slots): failed within
+                                                         # 20 steps before the slot-tenant fix (dm_tile_kernel.cuh, s_issued)
+                                                         ("humanoid3d", False, False, 3 << 20, 30)])
+def test_consecutive_steps_at_scale(robot, combined, soa, n, steps):
     import torch
     import bench
     from deepmimic_mujoco_b200.hotpath import HotPath
-    n, B, steps = 1 << 20, 2, 60
+    B = 2
     hp = HotPath(robot, combined=combined)
     hp.load_combined() if combined else hp.load_motions(["walk"])
     dev = torch.device("cuda", 0)
