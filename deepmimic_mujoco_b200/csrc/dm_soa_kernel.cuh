@@ -95,6 +95,8 @@ template <int KIND, class Rb> struct SoaGroups { static constexpr int G = 4; };
 // measured at 1 M / 262 144 envs: unitree_g1 DPEnv 272 us with four groups (128 registers, no spills) against 287 with three;
 // the combined env 300 / 94.5 us with four against 298 / 83.5 with three (its 57 KB slots leave the fourth group no slack)
 template <> struct SoaGroups<KIND_COMBINED, Robot_unitree_g1> { static constexpr int G = 3; };
+// (humanoid3d with three uncapped groups -- 149 registers, no spills -- was measured after the packed-arithmetic changes:
+// better at 262144 envs, 46.3 vs 49.1 us, equal at 1 M, worse at 65536 / 131072 / 524288: 19.2 / 29.4 / 85.2 vs 15.5 / 27.5 / 82.9 us)
 
 template <int KIND, class Rb, bool TERMS, bool STATS, bool TABLE_SMEM, int G>
 __global__ void __launch_bounds__(128 * G, 1) step_soa_kernel(const __grid_constant__ StepParams p, const SoaExtra x,
