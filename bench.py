@@ -38,6 +38,7 @@ NCU_TRAFFIC = {("humanoid3d", 0, 4096, "aos"): _t("h4096", 1.769728e6, 0.000000e
                ("humanoid3d", 0, 8192, "aos"): _t("c3_8192", 3.488512e6, 0.000000e6),
                ("humanoid3d", 0, 65536, "aos"): _t("c3_65536", 26.884864e6, 0.221696e6),
                ("humanoid3d", 0, 1048576, "aos"): _t("h1M", 444.581888e6, 362.651392e6),
+               ("humanoid3d", 0, 2097152, "aos"): _t("h2M", 887.202560e6, 779.940352e6),
                ("unitree_g1", 1, 32768, "aos"): _t("g1c_32768", 15.305216e6, 0.000000e6),
                ("unitree_g1", 1, 262144, "aos"): _t("g1c_262144", 120.935168e6, 95.656704e6),
                ("unitree_g1", 1, 1048576, "aos"): _t("g1c_1M", 535.478528e6, 536.336384e6),
